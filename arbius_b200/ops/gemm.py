@@ -1,0 +1,162 @@
+"""GEMM / conv wrappers over ``ab_gemm`` and ``ab_conv_direct`` (csrc/gemm_tc.cu, conv_direct.cu).
+
+Layouts (all channels-last):
+  linear   x [M, K]            w [N, K]                 -> [M, N]
+  conv3x3  x [B, H, W, C]      w [Cout, 3, 3, C] packed  -> [B, H, W, Cout]
+Weights arrive in their upstream layout (``nn.Linear`` [N, K], ``nn.Conv2d``
+[Cout, Cin, kh, kw]) and are repacked once at load time by ``pack_conv_weight`` /
+``pack_geglu_weight``; the checkpoint key layout on disk is untouched.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import native
+from .native import ACT, GemmArgs
+
+_workspaces: dict = {}
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    """Per-device split-K scratch, grown on demand (never shrinks, reused stream-ordered)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device())
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 24), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def pack_conv_weight(w: torch.Tensor) -> torch.Tensor:
+    """[Cout, Cin, kh, kw] (torch) -> [Cout, kh*kw*Cin] with K ordered (kh, kw, cin)."""
+    co, ci, kh, kw = w.shape
+    return w.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).contiguous()
+
+
+def pack_geglu_weight(w: torch.Tensor, b: Optional[torch.Tensor]):
+    """Interleave value/gate rows in blocks of 16 so one 32-column accumulator chunk holds
+    16 values and their 16 gates. w is the upstream ``GEGLU.proj`` weight [2*inner, K]
+    (first half values, second half gates)."""
+    two_inner, k = w.shape
+    inner = two_inner // 2
+    assert inner % 16 == 0, "GEGLU inner dim must be a multiple of 16"
+    val = w[:inner].reshape(inner // 16, 16, k)
+    gate = w[inner:].reshape(inner // 16, 16, k)
+    wp = torch.stack([val, gate], dim=1).reshape(two_inner, k).contiguous()
+    bp = None
+    if b is not None:
+        bp = torch.stack([b[:inner].reshape(-1, 16), b[inner:].reshape(-1, 16)], dim=1).reshape(two_inner).contiguous()
+    return wp, bp
+
+
+def auto_splitk(m: int, n: int, k_chunks: int, m_tiles: Optional[int] = None) -> int:
+    """Fixed, shape-only split-K choice (never depends on GPU count or load)."""
+    m_tiles = m_tiles if m_tiles is not None else (m + 127) // 128
+    tiles = m_tiles * ((n + 127) // 128)
+    if tiles >= 96 or k_chunks < 16:
+        return 1
+    s = min(8, max(1, 148 // tiles), k_chunks // 8)
+    return max(1, s)
+
+
+def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
+         x2: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+         rowbias: Optional[torch.Tensor] = None, rows_per_group: int = 0,
+         act: Optional[str] = None, geglu: bool = False, out_scale: float = 1.0,
+         out: Optional[torch.Tensor] = None, splitk: int = 0, block_n: int = 0) -> torch.Tensor:
+    """out = epilogue(cat[x, x2] @ w.T). x [..., K1], w [N, K1+K2]."""
+    lib = native.load()
+    lead = x.shape[:-1]
+    k1 = x.shape[-1]
+    xm = x.reshape(-1, k1)
+    assert xm.is_contiguous() and w.is_contiguous()
+    m = xm.shape[0]
+    n = w.shape[0]
+    k2 = 0
+    x2m = None
+    if x2 is not None:
+        k2 = x2.shape[-1]
+        x2m = x2.reshape(-1, k2)
+        assert x2m.is_contiguous() and x2m.shape[0] == m
+    assert w.shape[1] == k1 + k2, (w.shape, k1, k2)
+    nout = n // 2 if geglu else n
+    if out is None:
+        out = torch.empty((m, nout), dtype=x.dtype, device=x.device)
+    res = residual.reshape(-1, nout) if residual is not None else None
+    a = GemmArgs()
+    a.a, a.a2, a.w, a.out = xm.data_ptr(), native.ptr(x2m), w.data_ptr(), out.data_ptr()
+    a.bias, a.rowbias, a.residual = native.ptr(bias), native.ptr(rowbias), native.ptr(res)
+    a.M, a.N, a.K1, a.K2 = m, n, k1, k2
+    a.conv = 0
+    a.rows_per_group = rows_per_group
+    a.act, a.geglu, a.out_scale = ACT[act], int(geglu), out_scale
+    a.dtype = native.dtype_code(x.dtype)
+    a.block_n = block_n
+    a.ldo = out.stride(0) if out.dim() == 2 else 0
+    a.ldr = res.stride(0) if res is not None else 0
+    kc = (k1 + k2 + 63) // 64
+    a.splitk = splitk if splitk > 0 else auto_splitk(m, n, kc)
+    if a.splitk > 1:
+        a.workspace = _workspace(a.splitk * m * n * 4, x.device).data_ptr()
+    native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm")
+    return out.reshape(*lead, nout) if out.shape[0] == m and out.dim() == 2 else out
+
+
+def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
+            x2: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+            rowbias: Optional[torch.Tensor] = None, act: Optional[str] = None, out_scale: float = 1.0,
+            splitk: int = 0, block_n: int = 0) -> torch.Tensor:
+    """3x3 / pad 1 / stride 1 implicit-GEMM conv. x [B,H,W,C1] (+ x2 [B,H,W,C2]), w_packed [Cout, 9*(C1+C2)]."""
+    lib = native.load()
+    b, h, wd, c1 = x.shape
+    assert x.is_contiguous() and w_packed.is_contiguous()
+    c2 = x2.shape[-1] if x2 is not None else 0
+    n = w_packed.shape[0]
+    assert w_packed.shape[1] == 9 * (c1 + c2)
+    out = torch.empty((b, h, wd, n), dtype=x.dtype, device=x.device)
+    a = GemmArgs()
+    a.a, a.a2, a.w, a.out = x.data_ptr(), native.ptr(x2), w_packed.data_ptr(), out.data_ptr()
+    a.bias, a.rowbias, a.residual = native.ptr(bias), native.ptr(rowbias), native.ptr(residual)
+    a.M, a.N, a.K1, a.K2 = b * h * wd, n, c1, c2
+    a.conv, a.nimg, a.H, a.W = 1, b, h, wd
+    a.act, a.geglu, a.out_scale = ACT[act], 0, out_scale
+    a.dtype = native.dtype_code(x.dtype)
+    a.block_n = block_n
+    kc = 9 * (c1 + c2) // 64
+    a.splitk = splitk if splitk > 0 else auto_splitk(a.M, n, kc)
+    if a.splitk > 1:
+        a.workspace = _workspace(a.splitk * a.M * n * 4, x.device).data_ptr()
+    native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm(conv)")
+    return out
+
+
+def conv3x3_strided(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
+                    stride: int = 2, pad_mode: int = 0, act: Optional[str] = None) -> torch.Tensor:
+    """Strided 3x3 conv = gather (ab_im2col3x3) + tcgen05 GEMM. pad_mode 0: pad 1 all round; 1: right/bottom."""
+    lib = native.load()
+    b, h, wd, c = x.shape
+    ho = (h + (2 if pad_mode == 0 else 1) - 3) // stride + 1
+    wo = (wd + (2 if pad_mode == 0 else 1) - 3) // stride + 1
+    col = torch.empty((b * ho * wo, 9 * c), dtype=x.dtype, device=x.device)
+    native.check(lib.ab_im2col3x3(x.data_ptr(), col.data_ptr(), b, h, wd, c, stride, pad_mode,
+                                  native.dtype_code(x.dtype), native.stream_ptr()), "ab_im2col3x3")
+    y = gemm(col, w_packed, bias, act=act)
+    return y.reshape(b, ho, wo, -1)
+
+
+def conv_direct(x: torch.Tensor, w_khwc: torch.Tensor, bias: Optional[torch.Tensor] = None, *, ksize: int = 3,
+                stride: int = 1, act: Optional[str] = None) -> torch.Tensor:
+    """Small-channel conv. w_khwc is [Cout, kh, kw, Cin] contiguous (pack_conv_weight reshaped)."""
+    lib = native.load()
+    b, h, wd, cin = x.shape
+    cout = w_khwc.shape[0]
+    pad = ksize // 2
+    ho, wo = (h + 2 * pad - ksize) // stride + 1, (wd + 2 * pad - ksize) // stride + 1
+    out = torch.empty((b, ho, wo, cout), dtype=x.dtype, device=x.device)
+    native.check(lib.ab_conv_direct(x.data_ptr(), w_khwc.data_ptr(), native.ptr(bias), out.data_ptr(), b, h, wd, cin,
+                                    cout, ksize, stride, ACT[act], native.dtype_code(x.dtype), native.stream_ptr()),
+                 "ab_conv_direct")
+    return out

@@ -1,0 +1,519 @@
+// tcgen05 GEMM / implicit-GEMM 3x3 conv for sm_100a.
+//
+// One kernel serves every GEMM-shaped layer of the diffusion UNets, text encoders and VAEs:
+//   * linear / 1x1 conv:  A [M, K] row-major, loaded by a 2-D TMA tensor map
+//   * 3x3 conv (pad 1):   A is never materialised; each K step is one (tap, 64-channel) slab of
+//                         the NHWC image fetched by a 4-D TMA box whose start coordinate is shifted
+//                         by the tap offset — TMA's out-of-bounds zero fill IS the padding.
+//   * virtual concat:     a second A source appended along K (skip connections never get copied)
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
+// warps 2..5 = epilogue (tcgen05.ld -> bias/time-emb/activation/GEGLU/residual -> global).
+// Accumulators live in TMEM (128 lanes x BN fp32 columns). Two CTAs fit per SM (<=113 KB smem,
+// <=256 TMEM columns each) so one CTA's epilogue overlaps the other's main loop.
+// Split-K is a fixed, caller-chosen factor with an in-order second pass: results never depend on
+// scheduling, grid size or GPU count.
+#include <stdio.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "../include/arbius_b200.h"
+#include "common.cuh"
+
+extern "C" void ab_count_launch(int n);
+
+namespace ab {
+
+constexpr int BM = 128;      // rows per tile == TMEM lanes
+constexpr int BK = 64;       // 64 x 16-bit = one 128-byte swizzle row
+constexpr int UK = 16;       // K per tcgen05.mma for 16-bit inputs
+constexpr int GEMM_THREADS = 192;
+
+struct GemmParams {
+    void* out;
+    const void* bias;
+    const void* rowbias;
+    const void* residual;
+    float* workspace;
+    int M, N, Nout;
+    int k1_chunks, k2_chunks;   // 64-wide chunks from source 1 / source 2 (per tap in conv mode)
+    int taps;                   // 1 (linear) or 9 (conv)
+    int conv, nimg, H, W;
+    int bw_log2, bh_log2;       // conv tile: BW x BH x BI pixels, all powers of two, product 128
+    int tiles_w, tiles_h;
+    int rows_per_group;
+    int act, geglu;
+    float out_scale;
+    int splitk, chunks_per_split;
+    int ldo, ldr;
+};
+
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float (&f)[8]) {
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    unpack8<T>(v, f);
+}
+
+// Epilogue for one row x 32 accumulator columns starting at global column n_base.
+template <typename T>
+__device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long out_row, int grp, int n_base,
+                                                 float (&v)[32]) {
+    const T* bias = reinterpret_cast<const T*>(p.bias);
+    const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
+    const T* residual = reinterpret_cast<const T*>(p.residual);
+    T* out = reinterpret_cast<T*>(p.out);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const int n = n_base + 8 * g;
+        if (n < p.N) {
+            float b[8];
+            if (bias) {
+                load8<T>(bias + n, b);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[8 * g + i] += b[i];
+            }
+            if (rowbias) {
+                load8<T>(rowbias + static_cast<long long>(grp) * p.N + n, b);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[8 * g + i] += b[i];
+            }
+        }
+    }
+    if (p.geglu) {
+        // columns [0,16) are values, [16,32) the matching gates (weights were interleaved at load).
+        const int no = n_base >> 1;
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            const int n = no + 8 * g;
+            if (n < p.Nout) {
+                float o[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = v[8 * g + i] * act_gelu_erf(v[16 + 8 * g + i]) * p.out_scale;
+                if (residual) {
+                    float r[8];
+                    load8<T>(residual + out_row * p.ldr + n, r);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] += r[i];
+                }
+                *reinterpret_cast<uint4*>(out + out_row * p.ldo + n) = pack8<T>(o);
+            }
+        }
+        return;
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const int n = n_base + 8 * g;
+        if (n < p.N) {
+            float o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = apply_act(v[8 * g + i], p.act) * p.out_scale;
+            if (residual) {
+                float r[8];
+                load8<T>(residual + out_row * p.ldr + n, r);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] += r[i];
+            }
+            *reinterpret_cast<uint4*>(out + out_row * p.ldo + n) = pack8<T>(o);
+        }
+    }
+}
+
+template <int BN, int STAGES, typename T>
+__global__ void __launch_bounds__(GEMM_THREADS)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+               const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+    constexpr int A_BYTES = BM * BK * 2;
+    constexpr int B_BYTES = BN * BK * 2;
+    constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr int TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+    static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "UMMA N for M=128; epilogue reads 32-column chunks");
+    static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* acc_bar = empty_bar + STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    // ---- tile coordinates -------------------------------------------------------------------
+    const int tile_m = blockIdx.x;
+    const int n0 = blockIdx.y * BN;
+    int i0 = 0, h0 = 0, w0 = 0, m0 = 0;
+    if (p.conv) {
+        const int tw = tile_m % p.tiles_w;
+        const int th = (tile_m / p.tiles_w) % p.tiles_h;
+        const int ti = tile_m / (p.tiles_w * p.tiles_h);
+        w0 = tw << p.bw_log2;
+        h0 = th << p.bh_log2;
+        i0 = ti << (7 - p.bw_log2 - p.bh_log2);
+    } else {
+        m0 = tile_m * BM;
+    }
+    const int chunks_per_tap = p.k1_chunks + p.k2_chunks;
+    const int total_chunks = p.taps * chunks_per_tap;
+    const int kc_begin = blockIdx.z * p.chunks_per_split;
+    const int kc_end = min(total_chunks, kc_begin + p.chunks_per_split);
+
+    // ---- one-time setup ---------------------------------------------------------------------
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        if (p.k2_chunks) tma_prefetch_desc(&tmA2);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(acc_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kc = kc_begin; kc < kc_end; ++kc) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * STAGE_BYTES;
+                uint8_t* sb = sa + A_BYTES;
+                mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+                const int tap = kc / chunks_per_tap;
+                const int cc = kc - tap * chunks_per_tap;
+                const bool second = cc >= p.k1_chunks;
+                const CUtensorMap* ma = second ? &tmA2 : &tmA;
+                const int c0 = (second ? cc - p.k1_chunks : cc) * BK;
+                if (p.conv) {
+                    const int dh = tap / 3 - 1, dw = tap % 3 - 1;
+                    tma_load_4d(sa, ma, &full_bar[stage], c0, w0 + dw, h0 + dh, i0);
+                } else {
+                    tma_load_2d(sa, ma, &full_bar[stage], c0, m0);
+                }
+                tma_load_2d(sb, &tmB, &full_bar[stage], kc * BK, n0);
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer (one thread) =================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(BM, BN, DT<T>::kBf16, false, false);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kc = kc_begin; kc < kc_end; ++kc) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+                const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+                for (int k = 0; k < BK / UK; ++k) {
+                    const uint64_t adesc = make_smem_desc(sa + k * UK * 2, 16, 1024, kSwizzle128);
+                    const uint64_t bdesc = make_smem_desc(sb + k * UK * 2, 16, 1024, kSwizzle128);
+                    umma_ss(tmem_base, adesc, bdesc, idesc, (kc > kc_begin || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[stage]);   // frees this smem stage once the MMAs have read it
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(acc_bar);                 // accumulator complete
+        }
+    } else {
+        // ================= epilogue warps =================
+        const int q = warp & 3;                   // TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;              // row inside the tile
+        long long out_row;
+        int grp;
+        bool row_ok;
+        if (p.conv) {
+            const int wl = r & ((1 << p.bw_log2) - 1);
+            const int hl = (r >> p.bw_log2) & ((1 << p.bh_log2) - 1);
+            const int il = r >> (p.bw_log2 + p.bh_log2);
+            const int ww = w0 + wl, hh = h0 + hl, ii = i0 + il;
+            row_ok = (ww < p.W) && (hh < p.H) && (ii < p.nimg);
+            out_row = (static_cast<long long>(ii) * p.H + hh) * p.W + ww;
+            grp = ii;
+        } else {
+            out_row = m0 + r;
+            row_ok = out_row < p.M;
+            grp = p.rows_per_group > 0 ? static_cast<int>(out_row / p.rows_per_group) : 0;
+        }
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            uint32_t raw[32];
+            tmem_ld32(taddr + c * 32, raw);
+            tmem_wait_ld();
+            const int n_base = n0 + c * 32;
+            if (row_ok && n_base < p.N) {
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
+                if (p.splitk > 1) {
+                    float* ws = p.workspace + (static_cast<long long>(blockIdx.z) * p.M + out_row) * p.N + n_base;
+#pragma unroll
+                    for (int g = 0; g < 8; ++g)
+                        if (n_base + 4 * g < p.N)
+                            *reinterpret_cast<float4*>(ws + 4 * g) = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+                } else {
+                    epilogue_chunk32<T>(p, out_row, grp, n_base, v);
+                }
+            }
+        }
+    }
+
+    // ---- teardown -----------------------------------------------------------------------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+// Second pass of split-K: sum the fp32 partial tiles in split order, then the normal epilogue.
+template <typename T>
+__global__ void splitk_reduce_kernel(const GemmParams p) {
+    const int chunks_n = (p.N + 31) / 32;
+    const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= static_cast<long long>(p.M) * chunks_n) return;
+    const long long row = idx / chunks_n;
+    const int n_base = static_cast<int>(idx % chunks_n) * 32;
+    float v[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = 0.f;
+    for (int z = 0; z < p.splitk; ++z) {
+        const float* ws = p.workspace + (static_cast<long long>(z) * p.M + row) * p.N + n_base;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+            if (n_base + 4 * g < p.N) {
+                float4 t = *reinterpret_cast<const float4*>(ws + 4 * g);
+                v[4 * g] += t.x; v[4 * g + 1] += t.y; v[4 * g + 2] += t.z; v[4 * g + 3] += t.w;
+            }
+        }
+    }
+    const int grp = p.conv ? static_cast<int>(row / (static_cast<long long>(p.H) * p.W))
+                           : (p.rows_per_group > 0 ? static_cast<int>(row / p.rows_per_group) : 0);
+    epilogue_chunk32<T>(p, row, grp, n_base, v);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    });
+    return fn;
+}
+
+}  // namespace ab
+
+// Exposed for the other translation units (attention uses the same encoder).
+extern "C" int ab_make_tensor_map(CUtensorMap* out, int dtype, int rank, const void* base, const uint64_t* dims,
+                                  const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes) {
+    auto fn = ab::get_encode_fn();
+    if (!fn) { ab_set_error("cuTensorMapEncodeTiled entry point not available"); return -1; }
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+    CUresult r = fn(out, dtype == AB_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                    static_cast<cuuint32_t>(rank), const_cast<void*>(base), reinterpret_cast<const cuuint64_t*>(dims),
+                    reinterpret_cast<const cuuint64_t*>(strides_bytes), reinterpret_cast<const cuuint32_t*>(box), estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[256];
+        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled failed: CUresult %d (rank %d dims %llu,%llu box %u,%u)",
+                 static_cast<int>(r), rank, (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+                 box[0], rank > 1 ? box[1] : 0);
+        ab_set_error(buf);
+        return -1;
+    }
+    return 0;
+}
+
+namespace ab {
+
+static int ilog2(int v) { int l = 0; while ((1 << l) < v) ++l; return l; }
+
+struct ConvTile { int bw, bh, bi; };
+static ConvTile pick_conv_tile(int H, int W) {
+    // BW: power of two <= 128 with the least padding waste (ties -> larger)
+    int best_bw = 8; double best = 1e9;
+    for (int bw = 128; bw >= 8; bw >>= 1) {
+        double waste = double((W + bw - 1) / bw * bw) / W;
+        if (waste < best - 1e-9) { best = waste; best_bw = bw; }
+    }
+    int bh_max = 128 / best_bw;
+    int bh = 1;
+    while (bh < bh_max && bh < H) bh <<= 1;   // smallest pow2 >= H, capped
+    if (bh > bh_max) bh = bh_max;
+    return {best_bw, bh, 128 / (best_bw * bh)};
+}
+
+static int auto_block_n(int M_tiles, int N, bool geglu) {
+    // Prefer the tile width that fills 148 SMs x 2 resident CTAs with the least idle tail.
+    static const int cands[] = {256, 160, 128, 96, 64, 32};
+    int best = 64; double best_cost = 1e30;
+    for (int bn : cands) {
+        if (geglu && bn % 32) continue;
+        int tiles = M_tiles * ((N + bn - 1) / bn);
+        int slots = 148 * (bn > 160 ? 1 : 2);
+        int waves = (tiles + slots - 1) / slots;
+        // cost ~ waves x per-tile time (proportional to bn, plus a fixed overhead) incl. padded columns
+        double cost = waves * (bn + 48.0) * (bn > 160 ? 0.55 : 1.0);
+        if (cost < best_cost) { best_cost = cost; best = bn; }
+    }
+    return best;
+}
+
+template <int BN, int STAGES, typename T>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
+                       dim3 grid, cudaStream_t stream) {
+    constexpr int smem = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 16 + 1024;
+    static bool configured = false;
+    if (!configured) {
+        AB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+    }
+    gemm_tc_kernel<BN, STAGES, T><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmA2, tmB, p);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
+
+template <typename T>
+static int dispatch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                       const GemmParams& p, dim3 grid, cudaStream_t stream) {
+    switch (bn) {
+        case 32:  return launch_gemm<32, 4, T>(tmA, tmA2, tmB, p, grid, stream);
+        case 64:  return launch_gemm<64, 4, T>(tmA, tmA2, tmB, p, grid, stream);
+        case 96:  return launch_gemm<96, 3, T>(tmA, tmA2, tmB, p, grid, stream);
+        case 128: return launch_gemm<128, 3, T>(tmA, tmA2, tmB, p, grid, stream);
+        case 160: return launch_gemm<160, 3, T>(tmA, tmA2, tmB, p, grid, stream);
+        case 256: return launch_gemm<256, 4, T>(tmA, tmA2, tmB, p, grid, stream);
+        default: ab_set_error("unsupported block_n"); return -2;
+    }
+}
+
+}  // namespace ab
+
+extern "C" size_t ab_gemm_workspace_bytes(const ab_gemm_args* a) {
+    if (!a || a->splitk <= 1) return 0;
+    return static_cast<size_t>(a->splitk) * a->M * a->N * sizeof(float);
+}
+
+extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && a->a && a->w && a->out, "null pointer");
+    AB_REQUIRE(a->M > 0 && a->N > 0 && a->K1 > 0, "bad shape");
+    AB_REQUIRE(a->N % 8 == 0, "N must be a multiple of 8");
+    const int Ktot = a->K1 + a->K2;
+    AB_REQUIRE(Ktot % 8 == 0, "K must be a multiple of 8 (16-byte rows for TMA)");
+    if (a->K2 > 0) AB_REQUIRE(a->K1 % BK == 0 && a->a2, "virtual concat needs K1 % 64 == 0 and a2");
+    if (a->conv) AB_REQUIRE(a->K1 % BK == 0 && a->K2 % BK == 0, "conv needs channel counts that are multiples of 64");
+    if (a->conv) AB_REQUIRE(a->M == a->nimg * a->H * a->W, "conv: M != nimg*H*W");
+    if (a->geglu) AB_REQUIRE(a->N % 32 == 0, "geglu needs N % 32 == 0");
+
+    GemmParams p{};
+    p.out = a->out; p.bias = a->bias; p.rowbias = a->rowbias; p.residual = a->residual;
+    p.workspace = reinterpret_cast<float*>(a->workspace);
+    p.M = a->M; p.N = a->N; p.Nout = a->geglu ? a->N / 2 : a->N;
+    p.taps = a->conv ? 9 : 1;
+    p.k1_chunks = (a->K2 > 0 || a->conv) ? a->K1 / BK : (a->K1 + BK - 1) / BK;
+    p.k2_chunks = a->K2 > 0 ? (a->conv ? a->K2 / BK : (a->K2 + BK - 1) / BK) : 0;
+    p.conv = a->conv; p.nimg = a->nimg; p.H = a->H; p.W = a->W;
+    p.rows_per_group = a->conv ? a->H * a->W : a->rows_per_group;
+    p.act = a->act; p.geglu = a->geglu;
+    p.out_scale = a->out_scale == 0.f ? 1.f : a->out_scale;
+    p.ldo = a->ldo > 0 ? a->ldo : p.Nout;
+    p.ldr = a->ldr > 0 ? a->ldr : p.Nout;
+    AB_REQUIRE(p.ldo % 8 == 0 && p.ldr % 8 == 0, "row strides must be multiples of 8 elements");
+
+    int tiles_m;
+    ConvTile ct{128, 1, 1};
+    if (a->conv) {
+        ct = pick_conv_tile(a->H, a->W);
+        p.bw_log2 = ilog2(ct.bw); p.bh_log2 = ilog2(ct.bh);
+        p.tiles_w = (a->W + ct.bw - 1) / ct.bw;
+        p.tiles_h = (a->H + ct.bh - 1) / ct.bh;
+        tiles_m = p.tiles_w * p.tiles_h * ((a->nimg + ct.bi - 1) / ct.bi);
+    } else {
+        tiles_m = (a->M + BM - 1) / BM;
+    }
+    const int total_chunks = p.taps * (p.k1_chunks + p.k2_chunks);
+    int splitk = a->splitk > 1 ? a->splitk : 1;
+    if (splitk > total_chunks) splitk = total_chunks;
+    p.chunks_per_split = (total_chunks + splitk - 1) / splitk;
+    splitk = (total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;   // no empty splits
+    p.splitk = splitk;
+    if (splitk > 1) AB_REQUIRE(a->workspace, "split-K needs a workspace");
+
+    int bn = a->block_n > 0 ? a->block_n : auto_block_n(tiles_m * splitk, a->N, a->geglu != 0);
+
+    // ---- tensor maps ----
+    CUtensorMap tmA, tmA2, tmB;
+    const int esz = 2;
+    if (a->conv) {
+        uint64_t dims[4] = {(uint64_t)a->K1, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
+        uint64_t str[3] = {(uint64_t)a->K1 * esz, (uint64_t)a->W * a->K1 * esz, (uint64_t)a->H * a->W * a->K1 * esz};
+        uint32_t box[4] = {BK, (uint32_t)ct.bw, (uint32_t)ct.bh, (uint32_t)ct.bi};
+        if (ab_make_tensor_map(&tmA, a->dtype, 4, a->a, dims, str, box, 128)) return -1;
+        tmA2 = tmA;
+        if (a->K2 > 0) {
+            uint64_t dims2[4] = {(uint64_t)a->K2, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
+            uint64_t str2[3] = {(uint64_t)a->K2 * esz, (uint64_t)a->W * a->K2 * esz, (uint64_t)a->H * a->W * a->K2 * esz};
+            if (ab_make_tensor_map(&tmA2, a->dtype, 4, a->a2, dims2, str2, box, 128)) return -1;
+        }
+    } else {
+        uint64_t dims[2] = {(uint64_t)a->K1, (uint64_t)a->M};
+        uint64_t str[1] = {(uint64_t)a->K1 * esz};
+        uint32_t box[2] = {BK, BM};
+        if (ab_make_tensor_map(&tmA, a->dtype, 2, a->a, dims, str, box, 128)) return -1;
+        tmA2 = tmA;
+        if (a->K2 > 0) {
+            uint64_t dims2[2] = {(uint64_t)a->K2, (uint64_t)a->M};
+            uint64_t str2[1] = {(uint64_t)a->K2 * esz};
+            if (ab_make_tensor_map(&tmA2, a->dtype, 2, a->a2, dims2, str2, box, 128)) return -1;
+        }
+    }
+    {
+        const uint64_t Kw = (uint64_t)p.taps * Ktot;
+        uint64_t dims[2] = {Kw, (uint64_t)a->N};
+        uint64_t str[1] = {Kw * esz};
+        uint32_t box[2] = {BK, (uint32_t)bn};
+        if (ab_make_tensor_map(&tmB, a->dtype, 2, a->w, dims, str, box, 128)) return -1;
+    }
+
+    dim3 grid(tiles_m, (a->N + bn - 1) / bn, splitk);
+    int rc = a->dtype == AB_BF16 ? dispatch_bn<__nv_bfloat16>(bn, tmA, tmA2, tmB, p, grid, stream)
+                                 : dispatch_bn<__half>(bn, tmA, tmA2, tmB, p, grid, stream);
+    if (rc) return rc;
+    if (splitk > 1) {
+        const long long work = static_cast<long long>(p.M) * ((p.N + 31) / 32);
+        const int threads = 128;
+        const int blocks = static_cast<int>((work + threads - 1) / threads);
+        if (a->dtype == AB_BF16) splitk_reduce_kernel<__nv_bfloat16><<<blocks, threads, 0, stream>>>(p);
+        else splitk_reduce_kernel<__half><<<blocks, threads, 0, stream>>>(p);
+        AB_CHECK_CUDA(cudaGetLastError());
+        ab_count_launch(1);
+    }
+    return 0;
+}

@@ -1,0 +1,295 @@
+// GroupNorm(+SiLU) and LayerNorm on channels-last tensors.
+//
+// GroupNorm statistics follow the canonical 8-shard rule: the HW axis is cut into 8 row shards, each
+// shard into SUB blocks (SUB depends on HW only), every block reduces its rows in a fixed order to a
+// (sum, sumsq) pair per group in fp64, and the last block to finish combines all partials in
+// (shard, block) index order. Which block happens to be last does not matter: the combine order is
+// fixed, so the statistics are bit-identical for any grid size — and, with shards living on
+// different GPUs, for any GPU count.
+#include <stdio.h>
+
+#include "../include/arbius_b200.h"
+#include "common.cuh"
+
+extern "C" void ab_count_launch(int n);
+
+namespace ab {
+
+constexpr int GN_SHARDS = 8;
+constexpr int GN_MAX_SUB = 32;
+constexpr int GN_THREADS = 256;
+
+__host__ __device__ inline int gn_sub_blocks(int hw) {
+    int rows = (hw + GN_SHARDS - 1) / GN_SHARDS;
+    int sub = (rows + 63) / 64;
+    return sub < 1 ? 1 : (sub > GN_MAX_SUB ? GN_MAX_SUB : sub);
+}
+
+struct GnParams {
+    const void* x; const void* x2; void* y;
+    const void* gamma; const void* beta;
+    const void* scale; const void* shift;
+    double2* partials;     // [n][8][sub][groups]
+    float2* stats;         // [n][groups] (mean, rstd)
+    unsigned int* counters;  // [n]
+    int n, hw, c1, c2, groups, sub;
+    float eps;
+    int act;
+};
+
+// workspace layout: counters (n * 4 B, padded to 256) | stats (n*groups*8 B, padded to 256) | partials
+__host__ inline size_t gn_counters_bytes(int n) { return ((size_t)n * 4 + 255) / 256 * 256; }
+__host__ inline size_t gn_stats_bytes(int n, int groups) { return ((size_t)n * groups * 8 + 255) / 256 * 256; }
+
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) {
+    extern __shared__ float sm[];   // [2][RL][C]
+    __shared__ bool is_last;
+    const int C = p.c1 + p.c2;
+    const int ncol = C / 8;
+    const int cpg = C / p.groups;
+    const int n = blockIdx.z, shard = blockIdx.y, sub = blockIdx.x;
+    const int s_begin = static_cast<int>((static_cast<long long>(shard) * p.hw) / GN_SHARDS);
+    const int s_end = static_cast<int>((static_cast<long long>(shard + 1) * p.hw) / GN_SHARDS);
+    const int len = s_end - s_begin;
+    const int r0 = s_begin + static_cast<int>((static_cast<long long>(sub) * len) / p.sub);
+    const int r1 = s_begin + static_cast<int>((static_cast<long long>(sub + 1) * len) / p.sub);
+
+    const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
+    const int passes = (ncol + GN_THREADS - 1) / GN_THREADS;
+    float* s_sum = sm;
+    float* s_sq = sm + RL * C;
+    const T* x1 = reinterpret_cast<const T*>(p.x) + static_cast<long long>(n) * p.hw * p.c1;
+    const T* x2 = p.x2 ? reinterpret_cast<const T*>(p.x2) + static_cast<long long>(n) * p.hw * p.c2 : nullptr;
+
+    for (int pass = 0; pass < passes; ++pass) {
+        int vc, rl;
+        bool active;
+        if (passes == 1) { vc = threadIdx.x % ncol; rl = threadIdx.x / ncol; active = rl < RL; }
+        else { vc = pass * GN_THREADS + threadIdx.x; rl = 0; active = vc < ncol; }
+        if (active) {
+            const int c = vc * 8;
+            const T* src; int ld, cc;
+            if (c < p.c1) { src = x1; ld = p.c1; cc = c; } else { src = x2; ld = p.c2; cc = c - p.c1; }
+            float s[8], q[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
+            for (int r = r0 + rl; r < r1; r += RL) {
+                float f[8];
+                unpack8<T>(*reinterpret_cast<const uint4*>(src + static_cast<long long>(r) * ld + cc), f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { s_sum[rl * C + c + i] = s[i]; s_sq[rl * C + c + i] = q[i]; }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < p.groups) {
+        const int g = threadIdx.x;
+        double ds = 0.0, dq = 0.0;
+        for (int c = g * cpg; c < (g + 1) * cpg; ++c)
+            for (int rl = 0; rl < RL; ++rl) { ds += s_sum[rl * C + c]; dq += s_sq[rl * C + c]; }
+        p.partials[((static_cast<long long>(n) * GN_SHARDS + shard) * p.sub + sub) * p.groups + g] = make_double2(ds, dq);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int ticket = atomicAdd(&p.counters[n], 1u);
+        is_last = (ticket == static_cast<unsigned int>(GN_SHARDS * p.sub - 1));
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        if (threadIdx.x < p.groups) {
+            const int g = threadIdx.x;
+            double ds = 0.0, dq = 0.0;
+            const volatile double2* part = p.partials + static_cast<long long>(n) * GN_SHARDS * p.sub * p.groups;
+            for (int i = 0; i < GN_SHARDS * p.sub; ++i) {   // canonical (shard, block) order
+                ds += part[i * p.groups + g].x;
+                dq += part[i * p.groups + g].y;
+            }
+            const double cnt = static_cast<double>(p.hw) * cpg;
+            const double mean = ds / cnt;
+            double var = dq / cnt - mean * mean;
+            if (var < 0.0) var = 0.0;
+            p.stats[n * p.groups + g] = make_float2(static_cast<float>(mean),
+                                                     static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps))));
+        }
+        if (threadIdx.x == 0) p.counters[n] = 0;   // ready for the next call on this workspace
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) gn_apply_kernel(const GnParams p) {
+    const int C = p.c1 + p.c2;
+    const int ncol = C / 8;
+    const int cpg = C / p.groups;
+    const long long total = static_cast<long long>(p.n) * p.hw * ncol;
+    const T* gamma = reinterpret_cast<const T*>(p.gamma);
+    const T* beta = reinterpret_cast<const T*>(p.beta);
+    const T* scale = reinterpret_cast<const T*>(p.scale);
+    const T* shift = reinterpret_cast<const T*>(p.shift);
+    T* y = reinterpret_cast<T*>(p.y);
+    for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+         idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int vc = static_cast<int>(idx % ncol);
+        const long long row = idx / ncol;            // n*hw + r
+        const int n = static_cast<int>(row / p.hw);
+        const int c = vc * 8;
+        float f[8];
+        if (c < p.c1) unpack8<T>(*reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.x) + row * p.c1 + c), f);
+        else unpack8<T>(*reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.x2) + row * p.c2 + (c - p.c1)), f);
+        float ga[8], be[8];
+        if (gamma) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
+        if (beta) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(beta + c)), be);
+        float sc[8], sh[8];
+        if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * C + c)), sc);
+        if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * C + c)), sh);
+        const int g0 = c / cpg;
+        const float2 st0 = __ldg(&p.stats[n * p.groups + g0]);
+        const int g7 = (c + 7) / cpg;
+        float2 st1 = st0;
+        if (g7 != g0) st1 = __ldg(&p.stats[n * p.groups + g7]);   // 8 channels span at most 2 groups when cpg >= 8
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float2 st;
+            if (cpg >= 8) st = ((c + i) / cpg == g0) ? st0 : st1;
+            else st = __ldg(&p.stats[n * p.groups + (c + i) / cpg]);
+            float v = (f[i] - st.x) * st.y;
+            if (gamma) v *= ga[i];
+            if (beta) v += be[i];
+            if (scale) v *= (1.0f + sc[i]);
+            if (shift) v += sh[i];
+            o[i] = apply_act(v, p.act);
+        }
+        *reinterpret_cast<uint4*>(y + row * C + c) = pack8<T>(o);
+    }
+}
+
+// ---- LayerNorm: one warp per row, row held in registers -----------------------------------------
+template <typename T, int MAXV>
+__global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x, const T* __restrict__ gamma,
+                                                        const T* __restrict__ beta, T* __restrict__ y, int rows,
+                                                        int cols, float eps) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const int nvec = cols / 8;
+    const T* xr = x + static_cast<long long>(row) * cols;
+    float v[MAXV][8];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) {
+        const int vi = lane + 32 * j;
+        if (vi < nvec) {
+            unpack8<T>(*reinterpret_cast<const uint4*>(xr + vi * 8), v[j]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s += v[j][i];
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s / cols;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) {
+        const int vi = lane + 32 * j;
+        if (vi < nvec) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { const float d = v[j][i] - mean; q = fmaf(d, d, q); }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    const float rstd = rsqrtf(q / cols + eps);
+    T* yr = y + static_cast<long long>(row) * cols;
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) {
+        const int vi = lane + 32 * j;
+        if (vi < nvec) {
+            float ga[8], be[8], o[8];
+            if (gamma) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(gamma + vi * 8)), ga);
+            if (beta) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(beta + vi * 8)), be);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float t = (v[j][i] - mean) * rstd;
+                if (gamma) t *= ga[i];
+                if (beta) t += be[i];
+                o[i] = t;
+            }
+            *reinterpret_cast<uint4*>(yr + vi * 8) = pack8<T>(o);
+        }
+    }
+}
+
+}  // namespace ab
+
+extern "C" size_t ab_groupnorm_partials_bytes(int n, int groups) {
+    return ab::gn_counters_bytes(n) + ab::gn_stats_bytes(n, groups) +
+           static_cast<size_t>(n) * ab::GN_SHARDS * ab::GN_MAX_SUB * groups * sizeof(double2);
+}
+
+extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && a->x && a->y && a->partials, "null pointer (x, y and partials are required)");
+    const int C = a->c1 + a->c2;
+    AB_REQUIRE(a->n > 0 && a->hw > 0 && a->c1 > 0, "bad shape");
+    AB_REQUIRE(a->c1 % 8 == 0 && a->c2 % 8 == 0, "channel counts must be multiples of 8");
+    AB_REQUIRE(a->groups > 0 && a->groups <= GN_THREADS && C % a->groups == 0, "bad group count");
+    AB_REQUIRE(a->c2 == 0 || a->x2, "x2 missing");
+    AB_REQUIRE(a->hw >= GN_SHARDS || a->hw > 0, "bad hw");
+    GnParams p{};
+    p.x = a->x; p.x2 = a->x2; p.y = a->y; p.gamma = a->gamma; p.beta = a->beta; p.scale = a->scale; p.shift = a->shift;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(a->partials);
+    p.counters = reinterpret_cast<unsigned int*>(ws);
+    p.stats = reinterpret_cast<float2*>(ws + gn_counters_bytes(a->n));
+    p.partials = reinterpret_cast<double2*>(ws + gn_counters_bytes(a->n) + gn_stats_bytes(a->n, a->groups));
+    p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
+    p.sub = gn_sub_blocks(a->hw);
+    p.eps = a->eps; p.act = a->act;
+    const int ncol = C / 8;
+    const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
+    const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
+    AB_REQUIRE(smem <= 48 * 1024, "channel count too large for the stats kernel");
+    dim3 grid(p.sub, GN_SHARDS, a->n);
+    const long long total = static_cast<long long>(a->n) * a->hw * ncol;
+    int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148LL * 16));
+    if (a->dtype == AB_BF16) {
+        gn_stats_kernel<__nv_bfloat16><<<grid, GN_THREADS, smem, stream>>>(p);
+        gn_apply_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p);
+    } else {
+        gn_stats_kernel<__half><<<grid, GN_THREADS, smem, stream>>>(p);
+        gn_apply_kernel<__half><<<blocks, 256, 0, stream>>>(p);
+    }
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(2);
+    return 0;
+}
+
+extern "C" int ab_layernorm(const void* x, const void* gamma, const void* beta, void* y, int rows, int cols, float eps,
+                            int dtype, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(x && y && rows > 0 && cols > 0, "bad arguments");
+    AB_REQUIRE(cols % 8 == 0 && cols <= 32 * 8 * 16, "cols must be a multiple of 8 and <= 4096");
+    const int warps = 8;
+    const int blocks = (rows + warps - 1) / warps;
+    const int nvec = cols / 8;
+#define AB_LN(T, MAXV)                                                                                              \
+    layernorm_kernel<T, MAXV><<<blocks, warps * 32, 0, stream>>>(reinterpret_cast<const T*>(x),                    \
+                                                                  reinterpret_cast<const T*>(gamma),                \
+                                                                  reinterpret_cast<const T*>(beta),                 \
+                                                                  reinterpret_cast<T*>(y), rows, cols, eps)
+    if (dtype == AB_BF16) {
+        if (nvec <= 64) AB_LN(__nv_bfloat16, 2); else if (nvec <= 160) AB_LN(__nv_bfloat16, 5); else if (nvec <= 256) AB_LN(__nv_bfloat16, 8); else AB_LN(__nv_bfloat16, 16);
+    } else {
+        if (nvec <= 64) AB_LN(__half, 2); else if (nvec <= 160) AB_LN(__half, 5); else if (nvec <= 256) AB_LN(__half, 8); else AB_LN(__half, 16);
+    }
+#undef AB_LN
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

@@ -1,0 +1,140 @@
+/* arbius_b200 native C ABI (libarbius_b200.so, built from csrc/ for sm_100a).
+ *
+ * Conventions
+ *   - every entry point returns 0 on success, non-zero on error; ab_last_error() gives the text.
+ *   - `stream` is a cudaStream_t passed as void* (torch.cuda.current_stream().cuda_stream).
+ *   - activations are channels-last everywhere: images are [N, H, W, C], token tensors [M, C].
+ *   - dtype: 0 = fp16, 1 = bf16 (storage); accumulation and statistics are fp32.
+ *   - no entry point allocates device memory unless its comment says so: callers pass workspaces.
+ *   - reductions run in a fixed order that does not depend on grid size or GPU count
+ *     (the canonical 8-shard rule); there are no atomics on value paths.
+ *
+ * The reference has no native code: "ref" notes below name the op the external
+ * Cog containers would dispatch to (SURVEY §2.9 row ids K1..K17).
+ */
+#ifndef ARBIUS_B200_H
+#define ARBIUS_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* ab_last_error(void);
+int ab_version(void);
+/* number of kernel launches issued through this library since load (bench.py gpu_launches) */
+unsigned long long ab_launch_count(void);
+
+enum { AB_F16 = 0, AB_BF16 = 1 };
+enum {
+  AB_ACT_NONE = 0, AB_ACT_SILU = 1, AB_ACT_GELU = 2, AB_ACT_QUICK_GELU = 3, AB_ACT_GELU_TANH = 4,
+  AB_ACT_SIGMOID = 5, AB_ACT_TANH = 6, AB_ACT_RELU = 7, AB_ACT_HARDSWISH = 8, AB_ACT_HARDSIGMOID = 9,
+  AB_ACT_RELU6 = 10
+};
+
+/* ---- K2/K3/K1: tcgen05 GEMM / implicit-GEMM conv ------------------------------------------------
+ * out[M, Nout] = epilogue( A[M, K] * W[N, K]^T )
+ *   linear mode (conv == 0): A = a [M, K1] (and optionally a2 [M, K2] appended along K: virtual concat)
+ *   conv mode   (conv == 1): A is the implicit im2col of the NHWC image a [nimg, H, W, K1] (+ a2 with K2
+ *                channels, virtual channel concat) for a 3x3 / pad 1 / stride 1 kernel. M = nimg*H*W.
+ *                W is [N, 9*(K1+K2)] with K ordered (kh, kw, cin).
+ *   epilogue: v = acc + bias[n] + rowbias[m / rows_per_group, n]; v = act(v);
+ *             geglu: out[m, j] = v[value j] * gelu(v[gate j]) with value/gate columns interleaved in
+ *             blocks of 16 inside W (see ops/gemm.py: pack_geglu); Nout = N/2.
+ *             v = v * out_scale + residual[m, n]
+ *   splitk > 1: K is cut into `splitk` equal chunks, fp32 partial tiles go to `workspace`
+ *               (>= splitk*M*N*4 bytes) and are summed in split order by a second kernel.
+ * ref: cuBLAS HGEMM + ATen elementwise / cuDNN implicit GEMM conv.            */
+typedef struct {
+  const void* a; const void* a2; const void* w; void* out;
+  const void* bias; const void* rowbias; const void* residual;
+  void* workspace;
+  int M, N, K1, K2;
+  int conv, nimg, H, W;
+  int rows_per_group;       /* rows sharing one rowbias row (H*W for a time-embedding add) */
+  int act, geglu;
+  float out_scale;          /* 0 is treated as 1 */
+  int dtype;
+  int splitk;
+  int block_n;              /* 0 = auto; else one of 32, 64, 96, 128, 160, 256 */
+  int ldo;                  /* output row stride in elements, 0 = Nout */
+  int ldr;                  /* residual row stride in elements, 0 = Nout */
+} ab_gemm_args;
+int ab_gemm(const ab_gemm_args* args, void* stream);
+size_t ab_gemm_workspace_bytes(const ab_gemm_args* args);
+
+/* ---- K1 small-channel direct conv (conv_in / conv_out, Cin or Cout < 64) ------------------------ */
+/* x [N,H,W,Cin] -> out [N,Ho,Wo,Cout], weight [Cout, KH, KW, Cin], pad = KH/2, stride 1 or 2. */
+int ab_conv_direct(const void* x, const void* w, const void* bias, void* out, int n, int h, int wd, int cin,
+                   int cout, int ksize, int stride, int act, int dtype, void* stream);
+
+/* ---- K4: GroupNorm (+SiLU) on channels-last tensors --------------------------------------------
+ * x [N, HW, C1] (++ x2 [N, HW, C2] virtual channel concat) -> y [N, HW, C1+C2].
+ * Statistics: HW is cut into 8 canonical row shards; each shard is reduced by a fixed number of
+ * blocks in a fixed order, partials go to `partials` (>= ab_groupnorm_partials_bytes) and are
+ * combined in (shard, block) order by every apply block.  ref: ATen group_norm + silu.            */
+typedef struct {
+  const void* x; const void* x2; void* y;
+  const void* gamma; const void* beta;
+  void* partials;
+  int n, hw, c1, c2, groups;
+  float eps;
+  int act;
+  int dtype;
+  /* optional per-(n, channel) scale/shift applied after the affine: y = y*(1+scale)+shift */
+  const void* scale; const void* shift;
+} ab_groupnorm_args;
+int ab_groupnorm(const ab_groupnorm_args* args, void* stream);
+size_t ab_groupnorm_partials_bytes(int n, int groups);
+
+/* ---- K5: LayerNorm over the last dim ------------------------------------------------------------ */
+int ab_layernorm(const void* x, const void* gamma, const void* beta, void* y, int rows, int cols, float eps,
+                 int dtype, void* stream);
+
+/* ---- K6/K7: flash attention (tcgen05), q [B, Lq, H, D], k/v [B, Lk, H, D] token-major ------------
+ * strides are in elements: element (b, l, h, d) of q lives at q + b*q_bs + l*q_ls + h*D + d.       */
+typedef struct {
+  const void* q; const void* k; const void* v; void* out;
+  int batch, heads, lq, lk, head_dim;
+  long long q_bs, q_ls, k_bs, k_ls, v_bs, v_ls, o_bs, o_ls;
+  float scale;
+  int causal;
+  int dtype;
+} ab_attn_args;
+int ab_flash_attn(const ab_attn_args* args, void* stream);
+
+/* ---- K12/K15/G1/G3/S11: elementwise ------------------------------------------------------------- */
+/* counter-based N(0,1): out[i] = normal(philox4x32-10(seed, stream_id, offset + i)); i is the GLOBAL
+ * element index so any shard of the tensor draws the same values. out is fp32. */
+int ab_philox_normal(float* out, long long n, unsigned long long seed, unsigned long long stream_id,
+                     long long offset, void* stream);
+/* eps = uncond + g*(cond - uncond); x_out = ca*x + cb*eps + cc*aux + cn*noise (all fp32 math).
+ * eps_c/eps_u are model dtype [n]; x, aux, noise, x_out fp32; xm_out is x_out cast to model dtype. */
+int ab_cfg_step(const void* eps_c, const void* eps_u, const float* x, const float* aux, const float* noise,
+                float* x_out, void* xm_out, float* eps_out, long long n, float g, float ca, float cb, float cc,
+                float cn, int dtype, void* stream);
+/* (x/2+0.5).clamp(0,1)*255 -> uint8, NHWC in, NHWC (HWC) out; round-half-to-even */
+int ab_finalize_u8(const void* x, unsigned char* out, long long n, int dtype, void* stream);
+/* nearest-neighbour 2x upsample, NHWC */
+int ab_upsample_nearest2x(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
+/* bilinear resize NHWC (align_corners = 0 or 1) */
+int ab_resize_bilinear(const void* x, void* y, int n, int h, int w, int c, int oh, int ow, int align_corners,
+                       int dtype, void* stream);
+/* im2col gather for strided 3x3 conv: x [N,H,W,C] -> col [N*Ho*Wo, 9*C] (kh,kw,c), pad 1 */
+int ab_im2col3x3(const void* x, void* col, int n, int h, int w, int c, int stride, int pad_mode, int dtype,
+                 void* stream);
+/* y = act(a + b) or a*b etc.  op: 0 add, 1 mul, 2 a + b*s */
+int ab_binary(const void* a, const void* b, void* y, long long n, int op, float s, int act, int dtype,
+              void* stream);
+/* sinusoidal timestep embedding: out[b, dim] fp16/bf16, flip_sin_to_cos & freq_shift as in SD */
+int ab_timestep_embedding(const float* t, void* out, int batch, int dim, int flip_sin_to_cos, float freq_shift,
+                          float max_period, int dtype, void* stream);
+/* RVM: green-screen / alpha / foreground compositing, fgr [N,H,W,3], pha [N,H,W,1] -> u8 [N,H,W,3] */
+int ab_matting_composite(const void* fgr, const void* pha, unsigned char* out, long long npix, int mode,
+                         int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ARBIUS_B200_H */
