@@ -219,3 +219,37 @@ def test_elementwise(dt):
     freqs = torch.exp(-torch.log(torch.tensor(10000.0)) * torch.arange(half, device="cuda") / half)
     args = ts[:, None] * freqs[None]
     _close(te, torch.cat([args.cos(), args.sin()], -1), dt)
+
+
+def _attn_ref(q, k, v, scale=None, causal=False):
+    qf, kf, vf = (t.float().permute(0, 2, 1, 3) for t in (q, k, v))
+    o = F.scaled_dot_product_attention(qf, kf, vf, is_causal=causal, scale=scale)
+    return o.permute(0, 2, 1, 3)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("b,h,lq,lk,d,causal", [(2, 8, 4096, 4096, 40, False), (2, 8, 1024, 1024, 80, False),
+                                                 (2, 8, 256, 256, 160, False), (2, 8, 64, 64, 160, False),
+                                                 (2, 8, 4096, 77, 40, False), (2, 8, 1024, 77, 80, False),
+                                                 (2, 12, 77, 77, 64, True), (1, 5, 9216, 9216, 64, False),
+                                                 (3, 4, 300, 500, 64, False), (2, 2, 200, 200, 128, True)])
+def test_flash_attn(dt, b, h, lq, lk, d, causal):
+    from arbius_b200 import ops
+    q = torch.randn(b, lq, h, d, device="cuda", dtype=dt)
+    k = torch.randn(b, lk, h, d, device="cuda", dtype=dt)
+    v = torch.randn(b, lk, h, d, device="cuda", dtype=dt)
+    o = ops.flash_attn(q, k, v, causal=causal)
+    _close(o, _attn_ref(q, k, v, causal=causal), dt)
+    assert torch.equal(o, ops.flash_attn(q, k, v, causal=causal))
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_flash_attn_fused_qkv_views_and_large_logits(dt):
+    from arbius_b200 import ops
+    b, l, h, d = 2, 640, 8, 40
+    qkv = torch.randn(b, l, 3 * h * d, device="cuda", dtype=dt)
+    q, k, v = (qkv[..., i * h * d:(i + 1) * h * d].view(b, l, h, d) for i in range(3))
+    _close(ops.flash_attn(q, k, v), _attn_ref(q, k, v), dt)
+    # logits with a huge dynamic range exercise the lazy-rescale path
+    q2 = q * 6
+    _close(ops.flash_attn(q2, k, v), _attn_ref(q2, k, v), dt)
