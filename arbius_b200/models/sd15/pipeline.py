@@ -1,0 +1,250 @@
+"""Anything V3 (SD-1.5) txt2img pipeline: prompt -> uint8 image -> PNG bytes.
+
+Implements the work the reference delegates to the ``cjwbw/anything-v3-better-vae`` Cog container
+(reference: templates/anythingv3.json; request/response contract miner/src/index.ts:852-875):
+tokenise [negative, prompt] -> CLIP -> 20..N UNet steps at batch 2 with classifier-free guidance ->
+scheduler update -> VAE decode -> uint8 -> PNG.  Two backends share weights, tokenizer, RNG and the
+scheduler plans:
+
+  eager   torch modules (cuDNN / cuBLAS / ATen / SDPA): oracle on CPU fp32, timed baseline on GPU
+  native  the sm_100a kernels; the whole task (text encoder, every UNet step, sampler, VAE, uint8)
+          is captured once per (size, steps, sampler, guidance) into a single CUDA graph and
+          replayed per task: one H2D copy of token ids in, one D2H copy of pixels out.
+
+Initial latents and ancestral noise come from the global-index Philox stream (seed = taskid mod
+0x1FFFFFFFFFFFF0, reference: miner/src/utils.ts:15-19), laid out channels-last so row bands of the
+image are contiguous index ranges (patch-parallel shards draw identical values).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from ... import ops
+from ..schedulers import Scheduler, apply_plan_torch, make_scheduler
+from ..tokenizer import load_tokenizer
+from .clip_ref import CLIPTextModel, ClipTextConfig
+from .unet_ref import UNet2DConditionModel, UNetConfig, init_weights_
+from .vae_ref import AutoencoderKLDecoder, VaeConfig
+
+
+@dataclass
+class SD15Config:
+    unet: UNetConfig = field(default_factory=UNetConfig)
+    clip: ClipTextConfig = field(default_factory=ClipTextConfig)
+    vae: VaeConfig = field(default_factory=VaeConfig)
+
+    @staticmethod
+    def tiny() -> "SD15Config":
+        return SD15Config(UNetConfig.tiny(), ClipTextConfig.tiny(), VaeConfig.tiny())
+
+
+NOISE_STREAM_INIT = 0          # Philox stream ids: 0 = initial latents, 1 + i = ancestral noise of step i
+
+
+def build_modules(cfg: SD15Config, device="cpu", dtype=torch.float32, seed: int = 0):
+    """Random-init (no checkpoints offline) modules with upstream key layouts."""
+    with torch.device(device):
+        unet, clip, vae = UNet2DConditionModel(cfg.unet), CLIPTextModel(cfg.clip), AutoencoderKLDecoder(cfg.vae)
+    for i, m in enumerate((unet, clip, vae)):
+        init_weights_(m, seed + i)
+        m.to(dtype).eval().requires_grad_(False)
+    return unet, clip, vae
+
+
+def load_modules_from_dir(cfg: SD15Config, model_dir: str, device="cpu", dtype=torch.float32):
+    """Load diffusers-layout safetensors: <dir>/{unet,text_encoder,vae}/*.safetensors (keys unchanged)."""
+    from pathlib import Path
+
+    from safetensors.torch import load_file
+    unet, clip, vae = UNet2DConditionModel(cfg.unet), CLIPTextModel(cfg.clip), AutoencoderKLDecoder(cfg.vae)
+    for mod, sub in ((unet, "unet"), (clip, "text_encoder"), (vae, "vae")):
+        files = sorted((Path(model_dir) / sub).glob("*.safetensors"))
+        sd = {}
+        for f in files:
+            sd.update(load_file(str(f)))
+        own = mod.state_dict()
+        missing = [k for k in own if k not in sd]
+        if missing:
+            raise KeyError(f"{sub}: {len(missing)} tensors missing, e.g. {missing[:3]}")
+        mod.load_state_dict({k: sd[k] for k in own}, strict=True)
+        mod.to(device=device, dtype=dtype).eval().requires_grad_(False)
+    return unet, clip, vae
+
+
+class SD15Pipeline:
+    def __init__(self, cfg: SD15Config = SD15Config(), backend: str = "native", device: str = "cuda",
+                 dtype: torch.dtype = torch.float16, seed: int = 0, model_dir: Optional[str] = None,
+                 use_graph: bool = True):
+        self.cfg, self.backend, self.device, self.dtype = cfg, backend, torch.device(device), dtype
+        self.tokenizer = load_tokenizer(model_dir, cfg.clip.vocab_size)
+        if model_dir:
+            mods = load_modules_from_dir(cfg, model_dir, device, dtype)
+        else:
+            mods = build_modules(cfg, device, dtype, seed)
+        self.use_graph = use_graph and backend == "native"
+        self.vae_scale = 2 ** (len(cfg.vae.block_out_channels) - 1)      # 8 for the real model
+        self._graphs: Dict[Tuple, dict] = {}
+        if backend == "eager":
+            self.unet, self.clip, self.vae = mods
+        elif backend == "native":
+            from .native import NativeClipText, NativeUNet, NativeVaeDecoder
+            self.unet = NativeUNet(mods[0].state_dict(), cfg.unet, dtype, device)
+            self.clip = NativeClipText(mods[1].state_dict(), cfg.clip, dtype, device)
+            self.vae = NativeVaeDecoder(mods[2].state_dict(), cfg.vae, dtype, device)
+            del mods
+        else:
+            raise ValueError(backend)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # ------------------------------------------------------------------------------------------
+    def _token_ids(self, prompt: str, negative: str) -> torch.Tensor:
+        return torch.tensor([self.tokenizer.encode(negative), self.tokenizer.encode(prompt)], dtype=torch.int64)
+
+    def _noise(self, shape, seed: int, stream: int) -> torch.Tensor:
+        return ops.philox_normal(shape, seed, stream, 0, device=self.device)
+
+    # ------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def generate(self, prompt: str, negative_prompt: str = "", width: int = 512, height: int = 512,
+                 num_inference_steps: int = 20, guidance_scale: float = 7.5, scheduler: str = "DPMSolverMultistep",
+                 seed: int = 0) -> np.ndarray:
+        ids = self._token_ids(prompt, negative_prompt)
+        if self.backend == "eager":
+            return self._generate_eager(ids, width, height, num_inference_steps, guidance_scale, scheduler, seed)
+        return self._generate_native(ids, width, height, num_inference_steps, guidance_scale, scheduler, seed)
+
+    # ---------------- eager (oracle / baseline) ----------------
+    def _generate_eager(self, ids, width, height, steps, g, sched_name, seed) -> np.ndarray:
+        dev, dt = self.device, self.dtype
+        h, w = height // self.vae_scale, width // self.vae_scale
+        sch = make_scheduler(sched_name)
+        sch.set_timesteps(steps)
+        ids = ids.to(dev)
+        self.h2d_bytes = ids.numel() * 8
+        ctx = self.clip(ids)
+        x = self._noise((1, h, w, 4), seed, NOISE_STREAM_INIT).float() * sch.init_noise_sigma
+        bufs: Dict[str, torch.Tensor] = {"x": x}
+        for i, t in enumerate(sch.timesteps):
+            xin = (bufs["x"] * float(np.float32(sch.input_scale(i)))).to(dt).permute(0, 3, 1, 2).expand(2, -1, -1, -1)
+            tt = torch.full((2,), t, device=dev, dtype=torch.float32)
+            e = self.unet(xin.contiguous(), tt, ctx).permute(0, 2, 3, 1).float()
+            bufs["eps"] = e[0:1] + float(np.float32(g)) * (e[1:2] - e[0:1])
+            if sch.stochastic:
+                bufs["noise"] = self._noise((1, h, w, 4), seed, 1 + i).float()
+            apply_plan_torch(sch.plan(i), bufs)
+        img = self.vae(bufs["x"].to(dt).permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
+        u8 = ((img.float() / 2 + 0.5).clamp(0, 1) * 255).round().to(torch.uint8)[0]
+        out = u8.cpu().numpy()
+        self.d2h_bytes = out.size
+        return out
+
+    # ---------------- native ----------------
+    def _run_native(self, st: dict, sch: Scheduler, g: float) -> None:
+        """Everything between 'ids are on the device' and 'uint8 pixels are on the device'."""
+        dt = self.dtype
+        ctx = self.clip.forward(st["ids"])
+        kvs = self.unet.precompute_context(ctx)
+        temb = self.unet.time_projections(st["tvec"])          # [2*steps, sum(Cout)]
+        f = st["f32"]
+        ops.lincomb(f["x"], [(sch.init_noise_sigma, st["noise0"])])
+        n_steps = len(sch.timesteps)
+        for i in range(n_steps):
+            s_in = sch.input_scale(i)
+            for b in range(2):
+                ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=s_in)
+            e = self.unet.forward(st["xin"], temb[2 * i:2 * i + 2], kvs)
+            ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
+            for dst, terms in sch.plan(i):
+                srcs = [(c, st["noise"][i] if s == "noise" else f[s]) for c, s in terms]
+                ops.lincomb(f[dst], srcs)
+        ops.lincomb(None, [(1.0, f["x"])], dst_m=st["lat"], m_scale=1.0)
+        img = self.vae.forward(st["lat"])
+        st["u8"] = ops.finalize_u8(img)
+
+    def _state(self, key, width, height, steps, g, sched_name) -> dict:
+        st = self._graphs.get(key)
+        if st is not None:
+            return st
+        dev, dt = self.device, self.dtype
+        h, w = height // self.vae_scale, width // self.vae_scale
+        sch = make_scheduler(sched_name)
+        sch.set_timesteps(steps)
+        names = {"x", "eps", "tmp"} | set(sch.history)
+        st = dict(sch=sch,
+                  ids=torch.zeros((2, self.tokenizer.max_len), dtype=torch.int64, device=dev),
+                  ids_host=torch.zeros((2, self.tokenizer.max_len), dtype=torch.int64).pin_memory(),
+                  tvec=torch.tensor([t for t in sch.timesteps for _ in range(2)], dtype=torch.float32, device=dev),
+                  noise0=torch.zeros((1, h, w, 4), dtype=torch.float32, device=dev),
+                  noise=[torch.zeros((1, h, w, 4), dtype=torch.float32, device=dev) for _ in range(len(sch.timesteps))]
+                  if sch.stochastic else [],
+                  f32={n: torch.zeros((1, h, w, 4), dtype=torch.float32, device=dev) for n in names},
+                  xin=torch.zeros((2, h, w, 4), dtype=dt, device=dev),
+                  lat=torch.zeros((1, h, w, 4), dtype=dt, device=dev),
+                  out_host=torch.zeros((height, width, 3), dtype=torch.uint8).pin_memory(),
+                  graph=None, launches=0)
+        if self.use_graph:
+            # warm-up run on a side stream (allocator + lazy kernel attribute setup), then capture
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                self._run_native(st, sch, g)
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            n0 = ops.native.launch_count()
+            with torch.cuda.graph(graph):
+                self._run_native(st, sch, g)
+            st["launches"] = ops.native.launch_count() - n0
+            st["graph"] = graph
+        self._graphs[key] = st
+        return st
+
+    def _generate_native(self, ids, width, height, steps, g, sched_name, seed) -> np.ndarray:
+        key = (width, height, steps, float(g), sched_name)
+        st = self._state(key, width, height, steps, g, sched_name)
+        sch = st["sch"]
+        st["ids_host"].copy_(ids)
+        st["ids"].copy_(st["ids_host"], non_blocking=True)
+        self.h2d_bytes = ids.numel() * 8
+        h, w = height // self.vae_scale, width // self.vae_scale
+        lib = ops.native.load()
+        n = h * w * 4
+        ops.native.check(lib.ab_philox_normal(st["noise0"].data_ptr(), n, seed, NOISE_STREAM_INIT, 0,
+                                              ops.native.stream_ptr()), "philox")
+        for i, nb in enumerate(st["noise"]):
+            ops.native.check(lib.ab_philox_normal(nb.data_ptr(), n, seed, 1 + i, 0, ops.native.stream_ptr()), "philox")
+        if st["graph"] is not None:
+            st["graph"].replay()
+            self.last_launches = st["launches"] + 1 + len(st["noise"])
+        else:
+            n0 = ops.native.launch_count()
+            self._run_native(st, sch, g)
+            self.last_launches = ops.native.launch_count() - n0 + 1 + len(st["noise"])
+        st["out_host"].copy_(st["u8"][0], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        self.d2h_bytes = st["out_host"].numel()
+        return st["out_host"].numpy().copy()
+
+    # ------------------------------------------------------------------------------------------
+    def predict(self, inp: dict) -> bytes:
+        """Hydrated template input (+ integer ``seed``) -> PNG bytes of ``out-1.png``."""
+        from ...codecs.png import encode_png
+        img = self.generate(prompt=inp["prompt"], negative_prompt=inp.get("negative_prompt", "") or "",
+                            width=int(inp.get("width", 768)), height=int(inp.get("height", 768)),
+                            num_inference_steps=int(inp.get("num_inference_steps", 20)),
+                            guidance_scale=float(inp.get("guidance_scale", 12)),
+                            scheduler=inp.get("scheduler", "DPMSolverMultistep"), seed=int(inp.get("seed", 0)))
+        return encode_png(img)
+
+
+def smoke_step() -> None:
+    """One tiny end-to-end generation on cuda:0 through the native kernels (driver smoke test)."""
+    pipe = SD15Pipeline(SD15Config.tiny(), backend="native", device="cuda", dtype=torch.float16, use_graph=False)
+    img = pipe.generate("arbius test cat", "", 64, 64, 2, 7.5, "DPMSolverMultistep", seed=1337)
+    assert img.shape == (64, 64, 3) and img.dtype == np.uint8
+    torch.cuda.synchronize()

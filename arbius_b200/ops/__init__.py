@@ -1,7 +1,7 @@
 """Python face of the sm_100a kernels. Import is cheap; the shared library loads on first use."""
 from . import native
 from .attention import flash_attn
-from .elementwise import (binary, cfg_step, finalize_u8, matting_composite, philox_normal, philox_normal_cpu,
+from .elementwise import (binary, cfg_step, finalize_u8, lincomb, matting_composite, philox_normal, philox_normal_cpu,
                           philox_u32, resize_bilinear, timestep_embedding, upsample_nearest2x)
 from .gemm import (auto_splitk, conv3x3, conv3x3_strided, conv_direct, gemm, pack_conv_weight, pack_geglu_weight)
 from .norm import groupnorm, layernorm

@@ -82,6 +82,20 @@ def cfg_step(eps_c: torch.Tensor, eps_u: Optional[torch.Tensor], x: Optional[tor
     return x_out
 
 
+def lincomb(dst: Optional[torch.Tensor], terms, *, dst_m: Optional[torch.Tensor] = None, m_scale: float = 1.0):
+    """dst = sum coef*src over fp32 tensors (scheduler plan op). terms: [(coef, tensor), ...], <= 6."""
+    import ctypes as C
+    lib = native.load()
+    k = len(terms)
+    srcs = (C.c_void_p * k)(*[t.data_ptr() for _, t in terms])
+    coefs = (C.c_float * k)(*[float(c) for c, _ in terms])
+    n = terms[0][1].numel()
+    code = native.dtype_code(dst_m.dtype) if dst_m is not None else 0
+    native.check(lib.ab_lincomb(native.ptr(dst), native.ptr(dst_m), m_scale, srcs, coefs, k, n, code,
+                                native.stream_ptr()), "ab_lincomb")
+    return dst
+
+
 def finalize_u8(x: torch.Tensor) -> torch.Tensor:
     lib = native.load()
     out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)

@@ -97,6 +97,7 @@ def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
     a.block_n = block_n
     a.ldo = out.stride(0) if out.dim() == 2 else 0
     a.ldr = res.stride(0) if res is not None else 0
+    a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = (k1 + k2 + 63) // 64
     a.splitk = splitk if splitk > 0 else auto_splitk(m, n, kc)
     if a.splitk > 1:
@@ -125,6 +126,7 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     a.act, a.geglu, a.out_scale = ACT[act], 0, out_scale
     a.dtype = native.dtype_code(x.dtype)
     a.block_n = block_n
+    a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = 9 * (c1 + c2) // 64
     a.splitk = splitk if splitk > 0 else auto_splitk(a.M, n, kc)
     if a.splitk > 1:

@@ -37,6 +37,7 @@ class GemmArgs(C.Structure):
         ("block_n", C.c_int),
         ("ldo", C.c_int),
         ("ldr", C.c_int),
+        ("ldrb", C.c_int),
     ]
 
 
@@ -108,11 +109,15 @@ def load() -> C.CDLL:
     _sig(lib.ab_conv_direct, i, [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp])
     _sig(lib.ab_groupnorm, i, [C.POINTER(GroupNormArgs), vp])
     _sig(lib.ab_groupnorm_partials_bytes, C.c_size_t, [i, i])
+    _sig(lib.ab_softmax_rows, i, [vp, vp, i, i, f, i, vp])
+    _sig(lib.ab_transpose2d, i, [vp, vp, i, i, i, i, vp])
+    _sig(lib.ab_embedding, i, [vp, vp, vp, vp, i, i, i, i, vp])
     _sig(lib.ab_layernorm, i, [vp, vp, vp, vp, i, i, f, i, vp])
     if hasattr(lib, "ab_flash_attn"):
         _sig(lib.ab_flash_attn, i, [C.POINTER(AttnArgs), vp])
     _sig(lib.ab_philox_normal, i, [vp, ll, ull, ull, ll, vp])
     _sig(lib.ab_cfg_step, i, [vp, vp, vp, vp, vp, vp, vp, vp, ll, f, f, f, f, f, i, vp])
+    _sig(lib.ab_lincomb, i, [vp, vp, f, C.POINTER(vp), C.POINTER(f), i, ll, i, vp])
     _sig(lib.ab_finalize_u8, i, [vp, vp, ll, i, vp])
     _sig(lib.ab_upsample_nearest2x, i, [vp, vp, i, i, i, i, i, vp])
     _sig(lib.ab_resize_bilinear, i, [vp, vp, i, i, i, i, i, i, i, i, vp])

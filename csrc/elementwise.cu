@@ -215,6 +215,21 @@ __global__ void matting_composite_kernel(const T* __restrict__ fgr, const T* __r
     }
 }
 
+// dst = sum_k coef[k] * src[k] (fp32, left-to-right), optional model-dtype copy scaled by m_scale.
+struct LinCombArgs { const float* src[6]; float coef[6]; int n; };
+template <typename T>
+__global__ void lincomb_kernel(float* __restrict__ dst, T* __restrict__ dst_m, float m_scale, LinCombArgs a, long long n) {
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float acc = a.coef[0] * a.src[0][i];
+#pragma unroll
+        for (int k = 1; k < 6; ++k)
+            if (k < a.n) acc = acc + a.coef[k] * a.src[k][i];
+        if (dst) dst[i] = acc;
+        if (dst_m) dst_m[i] = DT<T>::from_f(acc * m_scale);
+    }
+}
+
 }  // namespace ab
 
 #define AB_DISPATCH(dtype, ...)                                 \
@@ -321,6 +336,19 @@ extern "C" int ab_matting_composite(const void* fgr, const void* pha, unsigned c
     AB_REQUIRE(fgr && pha && out && npix > 0, "bad arguments");
     AB_DISPATCH(dtype, (ab::matting_composite_kernel<T><<<ab::grid_for(npix, 256), 256, 0, stream>>>(
                            reinterpret_cast<const T*>(fgr), reinterpret_cast<const T*>(pha), out, npix, mode)));
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
+
+extern "C" int ab_lincomb(float* dst, void* dst_m, float m_scale, const float* const* srcs, const float* coefs, int nsrc,
+                          long long n, int dtype, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(nsrc >= 1 && nsrc <= 6 && n > 0 && (dst || dst_m), "bad arguments");
+    ab::LinCombArgs a{};
+    a.n = nsrc;
+    for (int k = 0; k < nsrc; ++k) { a.src[k] = srcs[k]; a.coef[k] = coefs[k]; }
+    AB_DISPATCH(dtype, (ab::lincomb_kernel<T><<<ab::grid_for(n, 256), 256, 0, stream>>>(dst, reinterpret_cast<T*>(dst_m), m_scale, a, n)));
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(1);
     return 0;

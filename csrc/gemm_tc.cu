@@ -45,7 +45,7 @@ struct GemmParams {
     int act, geglu;
     float out_scale;
     int splitk, chunks_per_split;
-    int ldo, ldr;
+    int ldo, ldr, ldrb;
 };
 
 template <typename T>
@@ -73,7 +73,7 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
                 for (int i = 0; i < 8; ++i) v[8 * g + i] += b[i];
             }
             if (rowbias) {
-                load8<T>(rowbias + static_cast<long long>(grp) * p.N + n, b);
+                load8<T>(rowbias + static_cast<long long>(grp) * p.ldrb + n, b);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[8 * g + i] += b[i];
             }
@@ -445,7 +445,8 @@ extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
     p.out_scale = a->out_scale == 0.f ? 1.f : a->out_scale;
     p.ldo = a->ldo > 0 ? a->ldo : p.Nout;
     p.ldr = a->ldr > 0 ? a->ldr : p.Nout;
-    AB_REQUIRE(p.ldo % 8 == 0 && p.ldr % 8 == 0, "row strides must be multiples of 8 elements");
+    p.ldrb = a->ldrb > 0 ? a->ldrb : a->N;
+    AB_REQUIRE(p.ldo % 8 == 0 && p.ldr % 8 == 0 && p.ldrb % 8 == 0, "row strides must be multiples of 8 elements");
 
     int tiles_m;
     ConvTile ct{128, 1, 1};

@@ -293,3 +293,117 @@ extern "C" int ab_layernorm(const void* x, const void* gamma, const void* beta, 
     ab_count_launch(1);
     return 0;
 }
+
+// ---- row softmax / transpose / embedding (small helpers around the GEMM-based wide-head attention) ----
+namespace ab {
+template <typename T>
+__global__ void __launch_bounds__(256) softmax_rows_kernel(const T* __restrict__ x, T* __restrict__ y, int rows, int cols,
+                                                           float scale) {
+    __shared__ float red[8];
+    const int row = blockIdx.x;
+    const T* xr = x + static_cast<long long>(row) * cols;
+    T* yr = y + static_cast<long long>(row) * cols;
+    const int nvec = cols / 8;
+    float mx = -INFINITY;
+    for (int v = threadIdx.x; v < nvec; v += 256) {
+        float f[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(xr + v * 8), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mx = fmaxf(mx, f[i] * scale);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    mx = red[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmaxf(mx, red[i]);
+    __syncthreads();
+    float sum = 0.f;
+    for (int v = threadIdx.x; v < nvec; v += 256) {
+        float f[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(xr + v * 8), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sum += __expf(f[i] * scale - mx);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sum += red[i];     // fixed order
+    const float inv = 1.f / sum;
+    for (int v = threadIdx.x; v < nvec; v += 256) {
+        float f[8], o[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(xr + v * 8), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = __expf(f[i] * scale - mx) * inv;
+        *reinterpret_cast<uint4*>(yr + v * 8) = pack8<T>(o);
+    }
+}
+
+template <typename T>
+__global__ void transpose2d_kernel(const T* __restrict__ x, T* __restrict__ y, int rows, int cols) {
+    __shared__ T tile[32][33];
+    const long long base = static_cast<long long>(blockIdx.z) * rows * cols;
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += 8) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        if (r < rows && c < cols) tile[i][threadIdx.x] = x[base + static_cast<long long>(r) * cols + c];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += 8) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (r < rows && c < cols) y[base + static_cast<long long>(c) * rows + r] = tile[threadIdx.x][i];
+    }
+}
+
+template <typename T>
+__global__ void embedding_kernel(const long long* __restrict__ ids, const T* __restrict__ tok, const T* __restrict__ pos,
+                                 T* __restrict__ out, int len, int dim) {
+    const int bl = blockIdx.x;
+    const int l = bl % len;
+    const long long id = ids[bl];
+    for (int v = threadIdx.x; v < dim / 8; v += blockDim.x) {
+        float a[8], b[8], o[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(tok + id * dim + v * 8), a);
+        unpack8<T>(*reinterpret_cast<const uint4*>(pos + static_cast<long long>(l) * dim + v * 8), b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = a[i] + b[i];
+        *reinterpret_cast<uint4*>(out + static_cast<long long>(bl) * dim + v * 8) = pack8<T>(o);
+    }
+}
+}  // namespace ab
+
+extern "C" int ab_softmax_rows(const void* x, void* y, int rows, int cols, float scale, int dtype, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(x && y && rows > 0 && cols % 8 == 0, "bad arguments");
+    if (dtype == AB_BF16) ab::softmax_rows_kernel<__nv_bfloat16><<<rows, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), rows, cols, scale);
+    else ab::softmax_rows_kernel<__half><<<rows, 256, 0, stream>>>(reinterpret_cast<const __half*>(x), reinterpret_cast<__half*>(y), rows, cols, scale);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
+
+extern "C" int ab_transpose2d(const void* x, void* y, int batch, int rows, int cols, int dtype, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(x && y && rows > 0 && cols > 0 && batch > 0, "bad arguments");
+    (void)dtype;   // 16-bit payload either way
+    dim3 grid((cols + 31) / 32, (rows + 31) / 32, batch), block(32, 8);
+    ab::transpose2d_kernel<__half><<<grid, block, 0, stream>>>(reinterpret_cast<const __half*>(x), reinterpret_cast<__half*>(y), rows, cols);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
+
+extern "C" int ab_embedding(const long long* ids, const void* tok, const void* pos, void* out, int batch, int len, int dim,
+                            int dtype, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(ids && tok && pos && out && dim % 8 == 0, "bad arguments");
+    if (dtype == AB_BF16) ab::embedding_kernel<__nv_bfloat16><<<batch * len, 128, 0, stream>>>(ids, reinterpret_cast<const __nv_bfloat16*>(tok), reinterpret_cast<const __nv_bfloat16*>(pos), reinterpret_cast<__nv_bfloat16*>(out), len, dim);
+    else ab::embedding_kernel<__half><<<batch * len, 128, 0, stream>>>(ids, reinterpret_cast<const __half*>(tok), reinterpret_cast<const __half*>(pos), reinterpret_cast<__half*>(out), len, dim);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

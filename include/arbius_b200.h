@@ -60,6 +60,7 @@ typedef struct {
   int block_n;              /* 0 = auto; else one of 32, 64, 96, 128, 160, 256 */
   int ldo;                  /* output row stride in elements, 0 = Nout */
   int ldr;                  /* residual row stride in elements, 0 = Nout */
+  int ldrb;                 /* rowbias row stride in elements, 0 = N */
 } ab_gemm_args;
 int ab_gemm(const ab_gemm_args* args, void* stream);
 size_t ab_gemm_workspace_bytes(const ab_gemm_args* args);
@@ -92,6 +93,14 @@ size_t ab_groupnorm_partials_bytes(int n, int groups);
 int ab_layernorm(const void* x, const void* gamma, const void* beta, void* y, int rows, int cols, float eps,
                  int dtype, void* stream);
 
+/* row softmax over the last dim (VAE single-head attention with head_dim 512), in place allowed */
+int ab_softmax_rows(const void* x, void* y, int rows, int cols, float scale, int dtype, void* stream);
+/* out[c, r] = x[r, c] for a [rows, cols] matrix (batched over `batch` matrices) */
+int ab_transpose2d(const void* x, void* y, int batch, int rows, int cols, int dtype, void* stream);
+/* token + position embedding gather: out[b, l, :] = tok[ids[b,l], :] + pos[l, :] */
+int ab_embedding(const long long* ids, const void* tok, const void* pos, void* out, int batch, int len, int dim,
+                 int dtype, void* stream);
+
 /* ---- K6/K7: flash attention (tcgen05), q [B, Lq, H, D], k/v [B, Lk, H, D] token-major ------------
  * strides are in elements: element (b, l, h, d) of q lives at q + b*q_bs + l*q_ls + h*D + d.       */
 typedef struct {
@@ -114,6 +123,10 @@ int ab_philox_normal(float* out, long long n, unsigned long long seed, unsigned 
 int ab_cfg_step(const void* eps_c, const void* eps_u, const float* x, const float* aux, const float* noise,
                 float* x_out, void* xm_out, float* eps_out, long long n, float g, float ca, float cb, float cc,
                 float cn, int dtype, void* stream);
+/* scheduler update: dst[i] = sum_k coefs[k]*srcs[k][i] (fp32, left to right, nsrc <= 6); dst_m (optional)
+ * receives dst*m_scale in the model dtype (the next step's scaled model input). dst may alias a source. */
+int ab_lincomb(float* dst, void* dst_m, float m_scale, const float* const* srcs, const float* coefs, int nsrc,
+               long long n, int dtype, void* stream);
 /* (x/2+0.5).clamp(0,1)*255 -> uint8, NHWC in, NHWC (HWC) out; round-half-to-even */
 int ab_finalize_u8(const void* x, unsigned char* out, long long n, int dtype, void* stream);
 /* nearest-neighbour 2x upsample, NHWC */
