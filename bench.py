@@ -1,0 +1,201 @@
+#!/usr/bin/env python
+"""Headline benchmark: Anything V3 (SD-1.5) txt2img 512x512, 20 steps, CFG -> tasks/hour + p50 latency.
+
+A "step" is one complete mining task: tokenise -> CLIP -> 20 UNet steps at batch 2 (classifier-free
+guidance) -> DPMSolver++ -> VAE decode -> uint8 image (-> PNG for the end-to-end number).
+N GPUs run independent tasks (task-level data parallelism, one process per GPU: weak scaling).
+
+  python bench.py --gpus 1 --steps 8 --warmup 3            # native sm_100a engine
+  python bench.py --impl eager ...                         # stock-library PyTorch restatement
+  python bench.py --impl reference ...                     # the reference itself (unavailable: TS/Solidity)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+METRIC = "tasks/hour + p50 task latency (AnythingV3 512^2, 20 steps, CFG)"
+
+
+def reference_arm() -> int:
+    why = ("mainnet-pat/arbius has no Python package or GPU code (TypeScript miner + Solidity; models run in "
+           "external Cog containers by docker digest): pip install of /root/reference fails "
+           "('neither setup.py nor pyproject.toml'), node/docker/network are absent")
+    print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [c.strip() for c in ln.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8, help="timed tasks per GPU")
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "eager", "reference"])
+    ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "tiny"])
+    ap.add_argument("--size", type=int, default=512)
+    ap.add_argument("--denoise-steps", type=int, default=20)
+    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm()
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    from arbius_b200 import ops
+    from arbius_b200.models.sd15.pipeline import SD15Config, SD15Pipeline
+    from arbius_b200.protocol import solution_cid
+
+    W = max(args.warmup, 3)
+    K = args.steps
+    dt = torch.float16 if args.dtype == "fp16" else torch.bfloat16
+    cfg = SD15Config() if args.model == "anythingv3" else SD15Config.tiny()
+    pipe = SD15Pipeline(cfg, backend=args.impl, device=f"cuda:{local}", dtype=dt, seed=0)
+    base = dict(prompt="arbius test cat, masterpiece, best quality", negative_prompt="lowres, bad anatomy",
+                width=args.size, height=args.size, num_inference_steps=args.denoise_steps, guidance_scale=12.0,
+                scheduler="DPMSolverMultistep")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_max(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- warm-up (graph capture happens here) ----
+    for i in range(W):
+        pipe.generate(seed=1000 + rank * 100 + i, **base)
+    barrier()
+
+    # ---- device-timed region: K tasks, CUDA events on the launching stream ----
+    n0 = ops.native.launch_count() if args.impl == "native" else 0
+    sampler = ClockSampler(local)
+    sampler.start()
+    lat = []
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(K):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        img = pipe.generate(seed=2000 + rank * 1000 + i, **base)
+        b.record()
+        lat.append((a, b))
+    ev1.record()
+    barrier()
+    dev_ms = reduce_max(ev0.elapsed_time(ev1))
+    lat_ms = sorted(a.elapsed_time(b) for a, b in lat)
+    clocks = sampler.stop()
+    launches = (getattr(pipe, "last_launches", 0) * K) if args.impl == "native" else 0
+    eager_launches = (ops.native.launch_count() - n0) if args.impl == "native" else 0
+
+    # ---- end-to-end: public API predict() -> PNG bytes (+ CID), pinned H2D in, D2H out, every task ----
+    barrier()
+    t0 = time.perf_counter()
+    cid = None
+    for i in range(K):
+        png = pipe.predict(dict(base, seed=3000 + rank * 1000 + i))
+        cid = solution_cid({"out-1.png": png})
+    torch.cuda.synchronize()
+    e2e_s = reduce_max(time.perf_counter() - t0)
+    barrier()
+
+    tasks_per_hour = world * K / (dev_ms / 1e3) * 3600.0
+    e2e_tph = world * K / e2e_s * 3600.0
+    weights_gb = 2 * (859.5 + 123.1 + 49.5) / 1e3 if args.model == "anythingv3" else 0.0
+    out = {
+        "metric": METRIC, "value": round(tasks_per_hour, 2), "unit": "tasks/hour", "impl": args.impl,
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(dev_ms / K, 3),
+        "p50_latency_ms": round(lat_ms[len(lat_ms) // 2], 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": args.dtype, "data": "synthetic prompts, random-init weights of the SD-1.5 architecture",
+        "config": {"model": "AnythingV3 (SD-1.5 UNet 860M + CLIP ViT-L/14 + AutoencoderKL)" if args.model == "anythingv3" else "tiny",
+                   "global_batch": world, "seq_len": 77, "image": f"{args.size}x{args.size}",
+                   "denoise_steps": args.denoise_steps, "cfg_batch": 2, "scheduler": "DPMSolverMultistep",
+                   "parallelism": f"task-dp{world}",
+                   "l2": f"inputs larger than L2: every task streams {weights_gb:.2f} GB of weights through a 126 MB L2"},
+        "clocks": clocks,
+        "e2e": {"value": round(e2e_tph, 2), "unit": "tasks/hour", "ms_per_task": round(e2e_s / K * 1e3, 3),
+                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
+                "includes": "tokenise, pinned H2D ids, Philox noise, graph replay, D2H pixels, PNG encode, CIDv0",
+                "last_cid": cid},
+        "gpu_launches": int(launches or eager_launches),
+    }
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
