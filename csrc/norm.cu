@@ -269,6 +269,104 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// ab_groupnorm_static: GroupNorm(+activation) for callers that must not allocate device memory.
+//
+// Who needs it: a host that has already given every free byte of HBM to its own arena (weights,
+// activations, KV) and has no allocator left to ask; a C or Rust caller that links this library
+// without torch and so has no caching allocator at all; a serving loop that cannot afford the
+// device-wide synchronisation a cudaMalloc/cudaFree implies while other tasks share the GPU.
+// For them the statistics scratch that ab_groupnorm takes from the caller lives here instead, in
+// a fixed array inside the library image. The price: every GPU that loads the library carries the
+// array (kStaticScratchBytes, about 0.5 MB) until the process exits, and the problem size is capped
+// at kStaticMaxImages images and kStaticMaxGroups groups per call.
+//
+// `g_gn_scratch` below is only a host-side handle when named in host code; the device address is
+// looked up with cudaGetSymbolAddress the first time the entry point runs on a device (with that
+// device current) and cached per device. Make that first call on each device outside any stream
+// capture. All calls share the one array and it keeps whatever the last call left in it, so the
+// block counters are cleared on the stream before every launch, and two calls that overlap on the
+// same GPU (different streams, or different host threads) race on it: serialise them.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace ab {
+constexpr int kStaticMaxImages = 4;
+constexpr int kStaticMaxGroups = 32;
+constexpr size_t kStaticCountersBytes = 256;                                   // >= 4 B x kStaticMaxImages
+constexpr size_t kStaticStatsBytes = 1024;                                     // 8 B x images x groups
+constexpr size_t kStaticPartialsBytes =
+    static_cast<size_t>(kStaticMaxImages) * GN_SHARDS * GN_MAX_SUB * kStaticMaxGroups * sizeof(double2);
+constexpr size_t kStaticScratchBytes = kStaticCountersBytes + kStaticStatsBytes + kStaticPartialsBytes;
+static_assert(kStaticCountersBytes >= kStaticMaxImages * sizeof(unsigned int), "counter region too small");
+static_assert(kStaticStatsBytes >= kStaticMaxImages * kStaticMaxGroups * sizeof(float2), "stats region too small");
+constexpr int kStaticMaxDevices = 64;
+}  // namespace ab
+
+static __device__ __align__(256) unsigned char g_gn_scratch[ab::kStaticScratchBytes];
+
+static std::mutex g_gn_static_mu;
+static unsigned char* g_gn_static_ptr[ab::kStaticMaxDevices] = {nullptr};
+
+extern "C" int ab_groupnorm_static(const ab_groupnorm_args* a, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && a->x && a->y, "null pointer (x and y are required)");
+    const int C = a->c1 + a->c2;
+    AB_REQUIRE(a->n > 0 && a->hw > 0 && a->c1 > 0, "bad shape");
+    AB_REQUIRE(a->n <= kStaticMaxImages,
+               "ab_groupnorm_static handles at most 4 images per call: split the batch or use ab_groupnorm");
+    AB_REQUIRE(a->groups > 0 && a->groups <= kStaticMaxGroups,
+               "ab_groupnorm_static handles at most 32 groups: use ab_groupnorm with a caller workspace");
+    AB_REQUIRE(a->c1 % 8 == 0 && a->c2 % 8 == 0, "channel counts must be multiples of 8");
+    AB_REQUIRE(C % a->groups == 0, "bad group count");
+    AB_REQUIRE(a->c2 == 0 || a->x2, "x2 missing");
+
+    // one-time set-up per device: resolve the device address of the scratch array
+    int dev = -1;
+    AB_CHECK_CUDA(cudaGetDevice(&dev));
+    AB_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "device index out of range");
+    unsigned char* ws = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_gn_static_mu);
+        if (g_gn_static_ptr[dev] == nullptr) {
+            unsigned char* sym = nullptr;
+            AB_CHECK_CUDA(cudaGetSymbolAddress((void**)&sym, g_gn_scratch));
+            AB_REQUIRE(sym != nullptr, "scratch symbol resolved to a null device address");
+            g_gn_static_ptr[dev] = sym;
+        }
+        ws = g_gn_static_ptr[dev];
+    }
+
+    GnParams p{};
+    p.x = a->x; p.x2 = a->x2; p.y = a->y; p.gamma = a->gamma; p.beta = a->beta; p.scale = a->scale; p.shift = a->shift;
+    p.counters = reinterpret_cast<unsigned int*>(ws);
+    p.stats = reinterpret_cast<float2*>(ws + kStaticCountersBytes);
+    p.partials = reinterpret_cast<double2*>(ws + kStaticCountersBytes + kStaticStatsBytes);
+    p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
+    p.sub = gn_sub_blocks(a->hw);
+    p.eps = a->eps; p.act = a->act;
+    const int ncol = C / 8;
+    const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
+    const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
+    AB_REQUIRE(smem <= 48 * 1024, "channel count too large for the stats kernel");
+    // the block tickets must start at zero whatever an earlier (possibly failed) call left behind
+    AB_CHECK_CUDA(cudaMemsetAsync(ws, 0, kStaticCountersBytes, stream));
+    dim3 grid(p.sub, GN_SHARDS, a->n);
+    const long long total = static_cast<long long>(a->n) * a->hw * ncol;
+    int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148LL * 16));
+    if (a->dtype == AB_BF16) {
+        gn_stats_kernel<__nv_bfloat16><<<grid, GN_THREADS, smem, stream>>>(p);
+        gn_apply_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p);
+    } else {
+        gn_stats_kernel<__half><<<grid, GN_THREADS, smem, stream>>>(p);
+        gn_apply_kernel<__half><<<blocks, 256, 0, stream>>>(p);
+    }
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(2);
+    return 0;
+}
+
 extern "C" int ab_layernorm(const void* x, const void* gamma, const void* beta, void* y, int rows, int cols, float eps,
                             int dtype, void* stream_) {
     using namespace ab;

@@ -88,6 +88,15 @@ typedef struct {
 } ab_groupnorm_args;
 int ab_groupnorm(const ab_groupnorm_args* args, void* stream);
 size_t ab_groupnorm_partials_bytes(int n, int groups);
+/* Same operation as ab_groupnorm for callers that cannot allocate device memory (a host whose arena
+ * already owns all of HBM, a plain C caller with no allocator, a loop that cannot take the device-wide
+ * sync of cudaMalloc). args->partials is ignored: the statistics scratch is a ~0.5 MB array compiled
+ * into the library, resident on every GPU that loads it until exit. Limits: n <= 4 images and
+ * groups <= 32 per call, otherwise an error is returned. The first call on each device resolves the
+ * array's device address; make that call outside any stream capture. All calls share the array: the
+ * counters are cleared on `stream` before each launch, and calls that overlap on one GPU race, so
+ * serialise them. Calls no cudaMalloc/cudaFree. No counterpart in the reference (it has no native code). */
+int ab_groupnorm_static(const ab_groupnorm_args* args, void* stream);
 
 /* ---- K5: LayerNorm over the last dim ------------------------------------------------------------ */
 int ab_layernorm(const void* x, const void* gamma, const void* beta, void* y, int rows, int cols, float eps,
