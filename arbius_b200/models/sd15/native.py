@@ -116,7 +116,7 @@ class NativeUNet:
         self.cfg, self.dtype, self.device = cfg, dtype, torch.device(device)
         g = lambda k: _get(sd, k, dtype, device)
         ch = cfg.block_out_channels
-        self.conv_in_w = g("conv_in.weight").permute(0, 2, 3, 1).contiguous()
+        self.conv_in_w = ops.DirectConvWeight(g("conv_in.weight").permute(0, 2, 3, 1))
         self.conv_in_b = g("conv_in.bias")
         self.te = (g("time_embedding.linear_1.weight"), g("time_embedding.linear_1.bias"),
                    g("time_embedding.linear_2.weight"), g("time_embedding.linear_2.bias"))
@@ -145,7 +145,7 @@ class NativeUNet:
                 blk["up"] = (ops.pack_conv_weight(g(p + "weight")), g(p + "bias"))
             self.up.append(blk)
         self.no_w, self.no_b = g("conv_norm_out.weight"), g("conv_norm_out.bias")
-        self.conv_out_w = g("conv_out.weight").permute(0, 2, 3, 1).contiguous()
+        self.conv_out_w = ops.DirectConvWeight(g("conv_out.weight").permute(0, 2, 3, 1))
         self.conv_out_b = g("conv_out.bias")
         # one fused time-embedding projection for every resnet
         res_all: List[_Resnet] = []
@@ -250,13 +250,13 @@ class NativeVaeDecoder:
         # post_quant_conv (1x1, lc->lc) padded to 8 output channels so the direct-conv kernel can vectorise
         pq = torch.zeros(8, 1, 1, lc, dtype=dtype, device=device)
         pq[:lc] = (g("post_quant_conv.weight") / cfg.scaling_factor).to(dtype).permute(0, 2, 3, 1)
-        self.pq_w = pq.contiguous()
+        self.pq_w = ops.DirectConvWeight(pq)
         self.pq_b = torch.zeros(8, dtype=dtype, device=device)
         self.pq_b[:lc] = g("post_quant_conv.bias")
         w = g("decoder.conv_in.weight").permute(0, 2, 3, 1)
         ci = torch.zeros(w.shape[0], 3, 3, 8, dtype=dtype, device=device)
         ci[..., :lc] = w
-        self.ci_w, self.ci_b = ci.contiguous(), g("decoder.conv_in.bias")
+        self.ci_w, self.ci_b = ops.DirectConvWeight(ci), g("decoder.conv_in.bias")
         gr = cfg.norm_groups
         mk_r = lambda p: _Resnet(sd, p, dtype, device, 1e-6, gr)
         self.mid_res = [mk_r("decoder.mid_block.resnets.0."), mk_r("decoder.mid_block.resnets.1.")]
@@ -275,7 +275,7 @@ class NativeVaeDecoder:
                 blk["up"] = (ops.pack_conv_weight(g(p + "weight")), g(p + "bias"))
             self.up.append(blk)
         self.no_w, self.no_b = g("decoder.conv_norm_out.weight"), g("decoder.conv_norm_out.bias")
-        self.co_w = g("decoder.conv_out.weight").permute(0, 2, 3, 1).contiguous()
+        self.co_w = ops.DirectConvWeight(g("decoder.conv_out.weight").permute(0, 2, 3, 1))
         self.co_b = g("decoder.conv_out.bias")
 
     def _attention(self, x: torch.Tensor) -> torch.Tensor:
@@ -302,7 +302,7 @@ class NativeVaeDecoder:
 
     def forward(self, latents: torch.Tensor) -> torch.Tensor:
         """latents [B, h, w, 4] (model dtype, channels-last, still scaled) -> image [B, 8h, 8w, 3] in [-1, 1]."""
-        z = ops.conv_direct(latents, self.pq_w, self.pq_b, ksize=1)
+        z = ops.conv_direct(latents, self.pq_w, self.pq_b)
         h = ops.conv_direct(z, self.ci_w, self.ci_b)
         h = self.mid_res[0](h, None)
         h = self._attention(h)

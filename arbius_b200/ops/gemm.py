@@ -10,6 +10,8 @@ Weights arrive in their upstream layout (``nn.Linear`` [N, K], ``nn.Conv2d``
 from __future__ import annotations
 
 import ctypes as C
+import json
+from pathlib import Path
 from typing import Optional
 
 import torch
@@ -18,6 +20,19 @@ from . import native
 from .native import ACT, GemmArgs
 
 _workspaces: dict = {}
+
+# Shape -> (block_n, splitk) choices measured on a B200 by scripts/tune_gemm.py. The table is part of the
+# source tree, so every box picks the same tiling for the same shape (bit-identical results everywhere).
+_TUNED_PATH = Path(__file__).with_name("tuned_sm100.json")
+_tuned: Optional[dict] = None
+RECORD: Optional[list] = None      # set to a list to log every (key, call kwargs) that goes through here
+
+
+def tuned_config(key: str):
+    global _tuned
+    if _tuned is None:
+        _tuned = json.loads(_TUNED_PATH.read_text()) if _TUNED_PATH.exists() else {}
+    return _tuned.get(key)
 
 
 def _workspace(nbytes: int, device) -> torch.Tensor:
@@ -99,7 +114,14 @@ def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
     a.ldr = res.stride(0) if res is not None else 0
     a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = (k1 + k2 + 63) // 64
-    a.splitk = splitk if splitk > 0 else auto_splitk(m, n, kc)
+    key = f"{'geglu' if geglu else 'lin'}:{m}:{n}:{k1 + k2}"
+    if RECORD is not None:
+        RECORD.append(key)
+    cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
+    if cfg is not None:
+        a.block_n, a.splitk = cfg[0], cfg[1]
+    else:
+        a.splitk = splitk if splitk > 0 else auto_splitk(m, n, kc)
     if a.splitk > 1:
         a.workspace = _workspace(a.splitk * m * n * 4, x.device).data_ptr()
     native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm")
@@ -128,7 +150,14 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     a.block_n = block_n
     a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = 9 * (c1 + c2) // 64
-    a.splitk = splitk if splitk > 0 else auto_splitk(a.M, n, kc)
+    key = f"conv:{b}x{h}x{wd}:{n}:{c1 + c2}"
+    if RECORD is not None:
+        RECORD.append(key)
+    cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
+    if cfg is not None:
+        a.block_n, a.splitk = cfg[0], cfg[1]
+    else:
+        a.splitk = splitk if splitk > 0 else auto_splitk(a.M, n, kc)
     if a.splitk > 1:
         a.workspace = _workspace(a.splitk * a.M * n * 4, x.device).data_ptr()
     native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm(conv)")
@@ -149,16 +178,30 @@ def conv3x3_strided(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torc
     return y.reshape(b, ho, wo, -1)
 
 
-def conv_direct(x: torch.Tensor, w_khwc: torch.Tensor, bias: Optional[torch.Tensor] = None, *, ksize: int = 3,
+class DirectConvWeight:
+    """Weight of a small-channel conv in the layout ab_conv_direct wants for its shape class:
+    [Cout, kh, kw, Cin] when Cout <= 8 (warp-per-pixel kernel), else [kh, kw, Cin, Cout]."""
+
+    def __init__(self, w_ohwi: torch.Tensor):
+        cout, kh, kw, cin = w_ohwi.shape
+        self.cout, self.cin, self.ks = cout, cin, kh
+        few_out = cout <= 8 and cin % 8 == 0
+        self.t = w_ohwi.contiguous() if few_out else w_ohwi.permute(1, 2, 3, 0).contiguous()
+
+
+def conv_direct(x: torch.Tensor, w, bias: Optional[torch.Tensor] = None, *, ksize: Optional[int] = None,
                 stride: int = 1, act: Optional[str] = None) -> torch.Tensor:
-    """Small-channel conv. w_khwc is [Cout, kh, kw, Cin] contiguous (pack_conv_weight reshaped)."""
+    """Small-channel conv. ``w`` is a DirectConvWeight (or a [Cout, kh, kw, Cin] tensor, packed on the fly)."""
     lib = native.load()
+    if not isinstance(w, DirectConvWeight):
+        w = DirectConvWeight(w)
     b, h, wd, cin = x.shape
-    cout = w_khwc.shape[0]
-    pad = ksize // 2
-    ho, wo = (h + 2 * pad - ksize) // stride + 1, (wd + 2 * pad - ksize) // stride + 1
+    assert cin == w.cin and (ksize is None or ksize == w.ks)
+    ks, cout = w.ks, w.cout
+    pad = ks // 2
+    ho, wo = (h + 2 * pad - ks) // stride + 1, (wd + 2 * pad - ks) // stride + 1
     out = torch.empty((b, ho, wo, cout), dtype=x.dtype, device=x.device)
-    native.check(lib.ab_conv_direct(x.data_ptr(), w_khwc.data_ptr(), native.ptr(bias), out.data_ptr(), b, h, wd, cin,
-                                    cout, ksize, stride, ACT[act], native.dtype_code(x.dtype), native.stream_ptr()),
+    native.check(lib.ab_conv_direct(x.data_ptr(), w.t.data_ptr(), native.ptr(bias), out.data_ptr(), b, h, wd, cin,
+                                    cout, ks, stride, ACT[act], native.dtype_code(x.dtype), native.stream_ptr()),
                  "ab_conv_direct")
     return out

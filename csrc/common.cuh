@@ -259,9 +259,9 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
 }
 
 // activations (fp32 math). Deterministic: no fast-math approximations that differ across builds.
-__device__ __forceinline__ float act_silu(float x) { return x / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float act_silu(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 __device__ __forceinline__ float act_gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
-__device__ __forceinline__ float act_quick_gelu(float x) { return x / (1.0f + __expf(-1.702f * x)); }
+__device__ __forceinline__ float act_quick_gelu(float x) { return __fdividef(x, 1.0f + __expf(-1.702f * x)); }
 __device__ __forceinline__ float act_gelu_tanh(float x) {
     const float k0 = 0.7978845608028654f, k1 = 0.044715f;
     return 0.5f * x * (1.0f + tanhf(k0 * (x + k1 * x * x * x)));
@@ -274,7 +274,7 @@ __device__ __forceinline__ float apply_act(float x, int act) {
         case ACT_GELU: return act_gelu_erf(x);
         case ACT_QUICK_GELU: return act_quick_gelu(x);
         case ACT_GELU_TANH: return act_gelu_tanh(x);
-        case ACT_SIGMOID: return 1.0f / (1.0f + __expf(-x));
+        case ACT_SIGMOID: return __fdividef(1.0f, 1.0f + __expf(-x));
         case ACT_TANH: return tanhf(x);
         case ACT_RELU: return fmaxf(x, 0.0f);
         case ACT_HARDSWISH: return x * fminf(fmaxf(x + 3.0f, 0.0f), 6.0f) * (1.0f / 6.0f);

@@ -35,6 +35,7 @@ struct GemmParams {
     const void* rowbias;
     const void* residual;
     float* workspace;
+    long long* dbg;             // optional per-CTA phase timestamps (debug/profiling only)
     int M, N, Nout;
     int k1_chunks, k2_chunks;   // 64-wide chunks from source 1 / source 2 (per tap in conv mode)
     int taps;                   // 1 (linear) or 9 (conv)
@@ -54,32 +55,53 @@ __device__ __forceinline__ void load8(const T* p, float (&f)[8]) {
     unpack8<T>(v, f);
 }
 
+// Epilogue modes are template parameters: a run-time switch per element made the epilogue ~100 KB of
+// branchy code that thrashed the instruction cache (10k cycles per 32-column chunk, measured).
+enum Epi : int { EPI_NONE = 0, EPI_SILU = 1, EPI_GELU = 2, EPI_QGELU = 3, EPI_GEGLU = 4, EPI_ANY = 5 };
+
+template <int EPI>
+__device__ __forceinline__ float epi_act(float x, int act) {
+    if constexpr (EPI == EPI_NONE) return x;
+    else if constexpr (EPI == EPI_SILU) return __fdividef(x, 1.0f + __expf(-x));
+    else if constexpr (EPI == EPI_GELU) return act_gelu_erf(x);
+    else if constexpr (EPI == EPI_QGELU) return __fdividef(x, 1.0f + __expf(-1.702f * x));
+    else return apply_act(x, act);
+}
+
 // Epilogue for one row x 32 accumulator columns starting at global column n_base.
-template <typename T>
+template <typename T, int EPI>
 __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long out_row, int grp, int n_base,
-                                                 float (&v)[32]) {
+                                                 float (&v)[32], const float* sb, bool rowbias_global) {
     const T* bias = reinterpret_cast<const T*>(p.bias);
     const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
     const T* residual = reinterpret_cast<const T*>(p.residual);
     T* out = reinterpret_cast<T*>(p.out);
+    if (sb) {
+        // bias (+ row bias when the tile sits in one group) was staged in shared memory during the main loop
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+            const float4 b4 = *reinterpret_cast<const float4*>(sb + 4 * g);
+            v[4 * g] += b4.x; v[4 * g + 1] += b4.y; v[4 * g + 2] += b4.z; v[4 * g + 3] += b4.w;
+        }
+    }
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
         const int n = n_base + 8 * g;
         if (n < p.N) {
             float b[8];
-            if (bias) {
+            if (bias && !sb) {
                 load8<T>(bias + n, b);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[8 * g + i] += b[i];
             }
-            if (rowbias) {
+            if (rowbias && rowbias_global) {
                 load8<T>(rowbias + static_cast<long long>(grp) * p.ldrb + n, b);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[8 * g + i] += b[i];
             }
         }
     }
-    if (p.geglu) {
+    if constexpr (EPI == EPI_GEGLU) {
         // columns [0,16) are values, [16,32) the matching gates (weights were interleaved at load).
         const int no = n_base >> 1;
 #pragma unroll
@@ -98,27 +120,27 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
                 *reinterpret_cast<uint4*>(out + out_row * p.ldo + n) = pack8<T>(o);
             }
         }
-        return;
-    }
+    } else {
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-        const int n = n_base + 8 * g;
-        if (n < p.N) {
-            float o[8];
+        for (int g = 0; g < 4; ++g) {
+            const int n = n_base + 8 * g;
+            if (n < p.N) {
+                float o[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) o[i] = apply_act(v[8 * g + i], p.act) * p.out_scale;
-            if (residual) {
-                float r[8];
-                load8<T>(residual + out_row * p.ldr + n, r);
+                for (int i = 0; i < 8; ++i) o[i] = epi_act<EPI>(v[8 * g + i], p.act) * p.out_scale;
+                if (residual) {
+                    float r[8];
+                    load8<T>(residual + out_row * p.ldr + n, r);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) o[i] += r[i];
+                    for (int i = 0; i < 8; ++i) o[i] += r[i];
+                }
+                *reinterpret_cast<uint4*>(out + out_row * p.ldo + n) = pack8<T>(o);
             }
-            *reinterpret_cast<uint4*>(out + out_row * p.ldo + n) = pack8<T>(o);
         }
     }
 }
 
-template <int BN, int STAGES, typename T>
+template <int BN, int STAGES, typename T, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
@@ -135,9 +157,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* acc_bar = empty_bar + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+    float* sbias = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot) + 4 + 15) & ~uintptr_t(15));  // [BN]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const long long t_start = p.dbg ? clock64() : 0;
+    long long* dbg = p.dbg ? p.dbg + 8LL * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
 
     // ---- tile coordinates -------------------------------------------------------------------
     const int tile_m = blockIdx.x;
@@ -175,6 +200,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (dbg && threadIdx.x == 32) dbg[0] = clock64() - t_start;   // setup done
 
     if (warp == 0) {
         // ================= TMA producer =================
@@ -210,6 +236,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int kc = kc_begin; kc < kc_end; ++kc) {
                 mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
+                if (dbg && kc == kc_begin) dbg[1] = clock64() - t_start;   // first operands landed
                 const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
                 const uint32_t sb = sa + A_BYTES;
 #pragma unroll
@@ -222,6 +249,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
             umma_commit(acc_bar);                 // accumulator complete
+            if (dbg) dbg[2] = clock64() - t_start;                     // all MMAs issued
         }
     } else {
         // ================= epilogue warps =================
@@ -243,10 +271,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             row_ok = out_row < p.M;
             grp = p.rows_per_group > 0 ? static_cast<int>(out_row / p.rows_per_group) : 0;
         }
+        // While the main loop runs, stage bias (+ row bias if the whole tile shares one group) in smem.
+        bool single_group;
+        int tile_grp;
+        if (p.conv) { single_group = (p.bw_log2 + p.bh_log2) == 7; tile_grp = i0; }
+        else if (p.rows_per_group > 0) {
+            const long long last = min(static_cast<long long>(m0) + BM - 1, static_cast<long long>(p.M) - 1);
+            tile_grp = m0 / p.rows_per_group;
+            single_group = (last / p.rows_per_group) == tile_grp;
+        } else { single_group = true; tile_grp = 0; }
+        const bool use_sb = p.splitk <= 1;
+        if (use_sb) {
+            const T* bias = reinterpret_cast<const T*>(p.bias);
+            const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
+            for (int n = threadIdx.x - 64; n < BN; n += 128) {
+                float b = 0.f;
+                if (n0 + n < p.N) {
+                    if (bias) b = DT<T>::to_f(bias[n0 + n]);
+                    if (rowbias && single_group) b += DT<T>::to_f(rowbias[static_cast<long long>(tile_grp) * p.ldrb + n0 + n]);
+                }
+                sbias[n] = b;
+            }
+            asm volatile("bar.sync 1, 128;\n" ::: "memory");
+        }
+        const bool rowbias_global = !single_group;
         mbar_wait(acc_bar, 0);
         tc_fence_after();
+        if (dbg && threadIdx.x == 64) dbg[3] = clock64() - t_start;   // accumulator ready
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-#pragma unroll 1
+#pragma unroll 2
         for (int c = 0; c < BN / 32; ++c) {
             uint32_t raw[32];
             tmem_ld32(taddr + c * 32, raw);
@@ -263,20 +316,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         if (n_base + 4 * g < p.N)
                             *reinterpret_cast<float4*>(ws + 4 * g) = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
                 } else {
-                    epilogue_chunk32<T>(p, out_row, grp, n_base, v);
+                    epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias + c * 32, rowbias_global);
                 }
             }
         }
     }
 
+    if (dbg && threadIdx.x == 64) dbg[4] = clock64() - t_start;       // epilogue done
     // ---- teardown -----------------------------------------------------------------------------
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+    if (dbg && threadIdx.x == 32) dbg[5] = clock64() - t_start;       // TMEM released
 }
 
 // Second pass of split-K: sum the fp32 partial tiles in split order, then the normal epilogue.
-template <typename T>
+template <typename T, int EPI>
 __global__ void splitk_reduce_kernel(const GemmParams p) {
     const int chunks_n = (p.N + 31) / 32;
     const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -298,7 +353,7 @@ __global__ void splitk_reduce_kernel(const GemmParams p) {
     }
     const int grp = p.conv ? static_cast<int>(row / (static_cast<long long>(p.H) * p.W))
                            : (p.rows_per_group > 0 ? static_cast<int>(row / p.rows_per_group) : 0);
-    epilogue_chunk32<T>(p, row, grp, n_base, v);
+    epilogue_chunk32<T, EPI>(p, row, grp, n_base, v, nullptr, true);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -383,36 +438,40 @@ static int auto_block_n(int M_tiles, int N, bool geglu) {
     return best;
 }
 
-template <int BN, int STAGES, typename T>
+template <int BN, int STAGES, typename T, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
                        dim3 grid, cudaStream_t stream) {
-    constexpr int smem = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 16 + 1024;
+    constexpr int smem = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 32 + BN * 4 + 1024;
     static bool configured = false;
     if (!configured) {
-        AB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        AB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, T, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
-    gemm_tc_kernel<BN, STAGES, T><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmA2, tmB, p);
+    gemm_tc_kernel<BN, STAGES, T, EPI><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmA2, tmB, p);
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(1);
     return 0;
 }
 
-template <typename T>
+template <typename T, int EPI>
 static int dispatch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                        const GemmParams& p, dim3 grid, cudaStream_t stream) {
     switch (bn) {
-        case 32:  return launch_gemm<32, 4, T>(tmA, tmA2, tmB, p, grid, stream);
-        case 64:  return launch_gemm<64, 4, T>(tmA, tmA2, tmB, p, grid, stream);
-        case 96:  return launch_gemm<96, 3, T>(tmA, tmA2, tmB, p, grid, stream);
-        case 128: return launch_gemm<128, 3, T>(tmA, tmA2, tmB, p, grid, stream);
-        case 160: return launch_gemm<160, 3, T>(tmA, tmA2, tmB, p, grid, stream);
-        case 256: return launch_gemm<256, 4, T>(tmA, tmA2, tmB, p, grid, stream);
+        case 32:  return launch_gemm<32, 4, T, EPI>(tmA, tmA2, tmB, p, grid, stream);
+        case 64:  return launch_gemm<64, 4, T, EPI>(tmA, tmA2, tmB, p, grid, stream);
+        case 96:  return launch_gemm<96, 3, T, EPI>(tmA, tmA2, tmB, p, grid, stream);
+        case 128: return launch_gemm<128, 3, T, EPI>(tmA, tmA2, tmB, p, grid, stream);
+        case 160: return launch_gemm<160, 3, T, EPI>(tmA, tmA2, tmB, p, grid, stream);
+        case 256: return launch_gemm<256, 4, T, EPI>(tmA, tmA2, tmB, p, grid, stream);
         default: ab_set_error("unsupported block_n"); return -2;
     }
 }
 
 }  // namespace ab
+
+static long long* g_gemm_dbg = nullptr;
+// Profiling aid: point at a device buffer of >= 8 * grid_size int64 to receive per-CTA phase cycle counts.
+extern "C" void ab_gemm_set_debug(long long* buf) { g_gemm_dbg = buf; }
 
 extern "C" size_t ab_gemm_workspace_bytes(const ab_gemm_args* a) {
     if (!a || a->splitk <= 1) return 0;
@@ -435,6 +494,7 @@ extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
     GemmParams p{};
     p.out = a->out; p.bias = a->bias; p.rowbias = a->rowbias; p.residual = a->residual;
     p.workspace = reinterpret_cast<float*>(a->workspace);
+    p.dbg = g_gemm_dbg;
     p.M = a->M; p.N = a->N; p.Nout = a->geglu ? a->N / 2 : a->N;
     p.taps = a->conv ? 9 : 1;
     p.k1_chunks = (a->K2 > 0 || a->conv) ? a->K1 / BK : (a->K1 + BK - 1) / BK;
@@ -504,15 +564,41 @@ extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
     }
 
     dim3 grid(tiles_m, (a->N + bn - 1) / bn, splitk);
-    int rc = a->dtype == AB_BF16 ? dispatch_bn<__nv_bfloat16>(bn, tmA, tmA2, tmB, p, grid, stream)
-                                 : dispatch_bn<__half>(bn, tmA, tmA2, tmB, p, grid, stream);
+    int epi = a->geglu ? EPI_GEGLU
+            : a->act == ACT_NONE ? EPI_NONE
+            : a->act == ACT_SILU ? EPI_SILU
+            : a->act == ACT_GELU ? EPI_GELU
+            : a->act == ACT_QUICK_GELU ? EPI_QGELU : EPI_ANY;
+    const int main_epi = splitk > 1 ? EPI_NONE : epi;     // with split-K the main kernel only stores fp32 partials
+    int rc;
+#define AB_GEMM_EPI(T)                                                                                     \
+    switch (main_epi) {                                                                                    \
+        case EPI_NONE: rc = dispatch_bn<T, EPI_NONE>(bn, tmA, tmA2, tmB, p, grid, stream); break;          \
+        case EPI_SILU: rc = dispatch_bn<T, EPI_SILU>(bn, tmA, tmA2, tmB, p, grid, stream); break;          \
+        case EPI_GELU: rc = dispatch_bn<T, EPI_GELU>(bn, tmA, tmA2, tmB, p, grid, stream); break;          \
+        case EPI_QGELU: rc = dispatch_bn<T, EPI_QGELU>(bn, tmA, tmA2, tmB, p, grid, stream); break;        \
+        case EPI_GEGLU: rc = dispatch_bn<T, EPI_GEGLU>(bn, tmA, tmA2, tmB, p, grid, stream); break;        \
+        default: rc = dispatch_bn<T, EPI_ANY>(bn, tmA, tmA2, tmB, p, grid, stream); break;                 \
+    }
+    if (a->dtype == AB_BF16) { AB_GEMM_EPI(__nv_bfloat16) } else { AB_GEMM_EPI(__half) }
+#undef AB_GEMM_EPI
     if (rc) return rc;
     if (splitk > 1) {
+        // one thread per (row, 32-column chunk); 64-thread blocks keep many CTAs in flight for small M*N
         const long long work = static_cast<long long>(p.M) * ((p.N + 31) / 32);
-        const int threads = 128;
+        const int threads = 64;
         const int blocks = static_cast<int>((work + threads - 1) / threads);
-        if (a->dtype == AB_BF16) splitk_reduce_kernel<__nv_bfloat16><<<blocks, threads, 0, stream>>>(p);
-        else splitk_reduce_kernel<__half><<<blocks, threads, 0, stream>>>(p);
+#define AB_RED_EPI(T)                                                                                      \
+    switch (epi) {                                                                                         \
+        case EPI_NONE: splitk_reduce_kernel<T, EPI_NONE><<<blocks, threads, 0, stream>>>(p); break;        \
+        case EPI_SILU: splitk_reduce_kernel<T, EPI_SILU><<<blocks, threads, 0, stream>>>(p); break;        \
+        case EPI_GELU: splitk_reduce_kernel<T, EPI_GELU><<<blocks, threads, 0, stream>>>(p); break;        \
+        case EPI_QGELU: splitk_reduce_kernel<T, EPI_QGELU><<<blocks, threads, 0, stream>>>(p); break;      \
+        case EPI_GEGLU: splitk_reduce_kernel<T, EPI_GEGLU><<<blocks, threads, 0, stream>>>(p); break;      \
+        default: splitk_reduce_kernel<T, EPI_ANY><<<blocks, threads, 0, stream>>>(p); break;               \
+    }
+        if (a->dtype == AB_BF16) { AB_RED_EPI(__nv_bfloat16) } else { AB_RED_EPI(__half) }
+#undef AB_RED_EPI
         AB_CHECK_CUDA(cudaGetLastError());
         ab_count_launch(1);
     }

@@ -2,8 +2,8 @@
 //
 // GroupNorm statistics follow the canonical 8-shard rule: the HW axis is cut into 8 row shards, each
 // shard into SUB blocks (SUB depends on HW only), every block reduces its rows in a fixed order to a
-// (sum, sumsq) pair per group in fp64, and the last block to finish combines all partials in
-// (shard, block) index order. Which block happens to be last does not matter: the combine order is
+// (count, mean, M2) triple per group, and the last block to finish merges all partials (Chan's parallel
+// variance update, fp32) in (shard, block) index order. Which block happens to be last does not matter: the combine order is
 // fixed, so the statistics are bit-identical for any grid size — and, with shards living on
 // different GPUs, for any GPU count.
 #include <stdio.h>
@@ -18,6 +18,7 @@ namespace ab {
 constexpr int GN_SHARDS = 8;
 constexpr int GN_MAX_SUB = 32;
 constexpr int GN_THREADS = 256;
+constexpr int GN_MAX_GROUPS = 64;
 
 __host__ __device__ inline int gn_sub_blocks(int hw) {
     int rows = (hw + GN_SHARDS - 1) / GN_SHARDS;
@@ -29,7 +30,7 @@ struct GnParams {
     const void* x; const void* x2; void* y;
     const void* gamma; const void* beta;
     const void* scale; const void* shift;
-    double2* partials;     // [n][8][sub][groups]
+    float4* partials;      // [n][8][sub][groups]  (count, mean, M2, -)
     float2* stats;         // [n][groups] (mean, rstd)
     unsigned int* counters;  // [n]
     int n, hw, c1, c2, groups, sub;
@@ -41,10 +42,25 @@ struct GnParams {
 __host__ inline size_t gn_counters_bytes(int n) { return ((size_t)n * 4 + 255) / 256 * 256; }
 __host__ inline size_t gn_stats_bytes(int n, int groups) { return ((size_t)n * groups * 8 + 255) / 256 * 256; }
 
+// Parallel-variance merge (Chan et al.): exact-order, fp32, no cancellation between blocks.
+struct GnMoments { float cnt, mean, m2; };
+__device__ __forceinline__ GnMoments gn_merge(const GnMoments a, const GnMoments b) {
+    if (b.cnt == 0.f) return a;
+    if (a.cnt == 0.f) return b;
+    GnMoments r;
+    r.cnt = a.cnt + b.cnt;
+    const float delta = b.mean - a.mean;
+    const float w = __fdividef(b.cnt, r.cnt);
+    r.mean = fmaf(delta, w, a.mean);
+    r.m2 = a.m2 + b.m2 + delta * delta * a.cnt * w;
+    return r;
+}
+
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) {
     extern __shared__ float sm[];   // [2][RL][C]
     __shared__ bool is_last;
+    __shared__ GnMoments shard_mom[GN_SHARDS][GN_MAX_GROUPS + 1];
     const int C = p.c1 + p.c2;
     const int ncol = C / 8;
     const int cpg = C / p.groups;
@@ -74,9 +90,33 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
             float s[8], q[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
-            for (int r = r0 + rl; r < r1; r += RL) {
+            const T* ptr = src + static_cast<long long>(r0 + rl) * ld + cc;
+            const long long step = static_cast<long long>(RL) * ld;
+            int r = r0 + rl;
+            for (; r + 3 * RL < r1; r += 4 * RL) {          // 4 independent loads in flight
+                uint4 v0 = *reinterpret_cast<const uint4*>(ptr);
+                uint4 v1 = *reinterpret_cast<const uint4*>(ptr + step);
+                uint4 v2 = *reinterpret_cast<const uint4*>(ptr + 2 * step);
+                uint4 v3 = *reinterpret_cast<const uint4*>(ptr + 3 * step);
+                ptr += 4 * step;
                 float f[8];
-                unpack8<T>(*reinterpret_cast<const uint4*>(src + static_cast<long long>(r) * ld + cc), f);
+                unpack8<T>(v0, f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                unpack8<T>(v1, f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                unpack8<T>(v2, f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                unpack8<T>(v3, f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+            }
+            for (; r < r1; r += RL) {
+                float f[8];
+                unpack8<T>(*reinterpret_cast<const uint4*>(ptr), f);
+                ptr += step;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
             }
@@ -87,10 +127,14 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
     __syncthreads();
     if (threadIdx.x < p.groups) {
         const int g = threadIdx.x;
-        double ds = 0.0, dq = 0.0;
-        for (int c = g * cpg; c < (g + 1) * cpg; ++c)
-            for (int rl = 0; rl < RL; ++rl) { ds += s_sum[rl * C + c]; dq += s_sq[rl * C + c]; }
-        p.partials[((static_cast<long long>(n) * GN_SHARDS + shard) * p.sub + sub) * p.groups + g] = make_double2(ds, dq);
+        float ds = 0.f, dq = 0.f;
+        for (int rl = 0; rl < RL; ++rl)
+            for (int c = g * cpg; c < (g + 1) * cpg; ++c) { ds += s_sum[rl * C + c]; dq += s_sq[rl * C + c]; }
+        const float cnt = static_cast<float>(r1 - r0) * cpg;
+        const float mean = cnt > 0.f ? ds / cnt : 0.f;
+        const float m2 = fmaxf(dq - ds * mean, 0.f);
+        p.partials[((static_cast<long long>(n) * GN_SHARDS + shard) * p.sub + sub) * p.groups + g] =
+            make_float4(cnt, mean, m2, 0.f);
     }
     __threadfence();
     __syncthreads();
@@ -101,70 +145,91 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
     __syncthreads();
     if (is_last) {
         __threadfence();
+        // level 1: thread (shard, g) merges that shard's blocks in index order; level 2: shards 0..7 in order
+        const volatile float4* part = p.partials + static_cast<long long>(n) * GN_SHARDS * p.sub * p.groups;
+        for (int idx = threadIdx.x; idx < GN_SHARDS * p.groups; idx += GN_THREADS) {
+            const int sh = idx / p.groups, g = idx % p.groups;
+            GnMoments acc{0.f, 0.f, 0.f};
+            for (int sb = 0; sb < p.sub; ++sb) {
+                const volatile float4* q4 = &part[(sh * p.sub + sb) * p.groups + g];
+                acc = gn_merge(acc, GnMoments{q4->x, q4->y, q4->z});
+            }
+            shard_mom[sh][g] = acc;
+        }
+        __syncthreads();
         if (threadIdx.x < p.groups) {
             const int g = threadIdx.x;
-            double ds = 0.0, dq = 0.0;
-            const volatile double2* part = p.partials + static_cast<long long>(n) * GN_SHARDS * p.sub * p.groups;
-            for (int i = 0; i < GN_SHARDS * p.sub; ++i) {   // canonical (shard, block) order
-                ds += part[i * p.groups + g].x;
-                dq += part[i * p.groups + g].y;
-            }
-            const double cnt = static_cast<double>(p.hw) * cpg;
-            const double mean = ds / cnt;
-            double var = dq / cnt - mean * mean;
-            if (var < 0.0) var = 0.0;
-            p.stats[n * p.groups + g] = make_float2(static_cast<float>(mean),
-                                                     static_cast<float>(1.0 / sqrt(var + static_cast<double>(p.eps))));
+            GnMoments acc = shard_mom[0][g];
+#pragma unroll
+            for (int sh = 1; sh < GN_SHARDS; ++sh) acc = gn_merge(acc, shard_mom[sh][g]);
+            const float var = acc.m2 / acc.cnt;
+            p.stats[n * p.groups + g] = make_float2(acc.mean, rsqrtf(var + p.eps));
         }
         if (threadIdx.x == 0) p.counters[n] = 0;   // ready for the next call on this workspace
     }
 }
 
+// y = act((x - mean) * rstd * gamma + beta [ * (1 + scale) + shift ]): per-thread channel vector is fixed, so
+// the affine is folded once into (a, b) and every row costs one 16-byte load, 8 FMAs and one 16-byte store.
+constexpr int GN_APPLY_ROWS = 8;   // rows per thread
 template <typename T>
-__global__ void __launch_bounds__(256) gn_apply_kernel(const GnParams p) {
+__global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const GnParams p) {
     const int C = p.c1 + p.c2;
     const int ncol = C / 8;
     const int cpg = C / p.groups;
-    const long long total = static_cast<long long>(p.n) * p.hw * ncol;
+    const int n = blockIdx.y;
+    const int cols = ncol < GN_THREADS ? ncol : GN_THREADS;
+    const int RL = GN_THREADS / cols;
+    const int passes = (ncol + cols - 1) / cols;
+    const int rl = threadIdx.x / cols;
+    if (rl >= RL) return;
+    const int r_begin = blockIdx.x * (RL * GN_APPLY_ROWS);
+    const int r_end = min(p.hw, r_begin + RL * GN_APPLY_ROWS);
     const T* gamma = reinterpret_cast<const T*>(p.gamma);
     const T* beta = reinterpret_cast<const T*>(p.beta);
     const T* scale = reinterpret_cast<const T*>(p.scale);
     const T* shift = reinterpret_cast<const T*>(p.shift);
-    T* y = reinterpret_cast<T*>(p.y);
-    for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
-         idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-        const int vc = static_cast<int>(idx % ncol);
-        const long long row = idx / ncol;            // n*hw + r
-        const int n = static_cast<int>(row / p.hw);
+    T* y = reinterpret_cast<T*>(p.y) + static_cast<long long>(n) * p.hw * C;
+    for (int pass = 0; pass < passes; ++pass) {
+        const int vc = pass * cols + threadIdx.x % cols;
+        if (vc >= ncol) continue;
         const int c = vc * 8;
-        float f[8];
-        if (c < p.c1) unpack8<T>(*reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.x) + row * p.c1 + c), f);
-        else unpack8<T>(*reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.x2) + row * p.c2 + (c - p.c1)), f);
-        float ga[8], be[8];
-        if (gamma) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
-        if (beta) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(beta + c)), be);
-        float sc[8], sh[8];
-        if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * C + c)), sc);
-        if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * C + c)), sh);
-        const int g0 = c / cpg;
-        const float2 st0 = __ldg(&p.stats[n * p.groups + g0]);
-        const int g7 = (c + 7) / cpg;
-        float2 st1 = st0;
-        if (g7 != g0) st1 = __ldg(&p.stats[n * p.groups + g7]);   // 8 channels span at most 2 groups when cpg >= 8
-        float o[8];
+        const T* src; int ld, cc;
+        if (c < p.c1) { src = reinterpret_cast<const T*>(p.x) + static_cast<long long>(n) * p.hw * p.c1; ld = p.c1; cc = c; }
+        else { src = reinterpret_cast<const T*>(p.x2) + static_cast<long long>(n) * p.hw * p.c2; ld = p.c2; cc = c - p.c1; }
+        float a[8], b[8];
+        {
+            float ga[8], be[8], sc[8], sh[8];
+            if (gamma) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
+            if (beta) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(beta + c)), be);
+            if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * C + c)), sc);
+            if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * C + c)), sh);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float2 st;
-            if (cpg >= 8) st = ((c + i) / cpg == g0) ? st0 : st1;
-            else st = __ldg(&p.stats[n * p.groups + (c + i) / cpg]);
-            float v = (f[i] - st.x) * st.y;
-            if (gamma) v *= ga[i];
-            if (beta) v += be[i];
-            if (scale) v *= (1.0f + sc[i]);
-            if (shift) v += sh[i];
-            o[i] = apply_act(v, p.act);
+            for (int i = 0; i < 8; ++i) {
+                const float2 st = __ldg(&p.stats[n * p.groups + (c + i) / cpg]);
+                float ai = st.y, bi = -st.x * st.y;
+                if (gamma) { ai *= ga[i]; bi *= ga[i]; }
+                if (beta) bi += be[i];
+                if (scale) { ai *= (1.0f + sc[i]); bi *= (1.0f + sc[i]); }
+                if (shift) bi += sh[i];
+                a[i] = ai; b[i] = bi;
+            }
         }
-        *reinterpret_cast<uint4*>(y + row * C + c) = pack8<T>(o);
+        for (int r = r_begin + rl; r < r_end; r += RL) {
+            float f[8], o[8];
+            unpack8<T>(*reinterpret_cast<const uint4*>(src + static_cast<long long>(r) * ld + cc), f);
+            if (p.act == ACT_SILU) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = act_silu(fmaf(f[i], a[i], b[i]));
+            } else if (p.act == ACT_NONE) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = fmaf(f[i], a[i], b[i]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = apply_act(fmaf(f[i], a[i], b[i]), p.act);
+            }
+            *reinterpret_cast<uint4*>(y + static_cast<long long>(r) * C + c) = pack8<T>(o);
+        }
     }
 }
 
@@ -238,7 +303,7 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     const int C = a->c1 + a->c2;
     AB_REQUIRE(a->n > 0 && a->hw > 0 && a->c1 > 0, "bad shape");
     AB_REQUIRE(a->c1 % 8 == 0 && a->c2 % 8 == 0, "channel counts must be multiples of 8");
-    AB_REQUIRE(a->groups > 0 && a->groups <= GN_THREADS && C % a->groups == 0, "bad group count");
+    AB_REQUIRE(a->groups > 0 && a->groups <= GN_MAX_GROUPS && C % a->groups == 0, "bad group count (1..64, dividing C)");
     AB_REQUIRE(a->c2 == 0 || a->x2, "x2 missing");
     AB_REQUIRE(a->hw >= GN_SHARDS || a->hw > 0, "bad hw");
     GnParams p{};
@@ -246,7 +311,7 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     uint8_t* ws = reinterpret_cast<uint8_t*>(a->partials);
     p.counters = reinterpret_cast<unsigned int*>(ws);
     p.stats = reinterpret_cast<float2*>(ws + gn_counters_bytes(a->n));
-    p.partials = reinterpret_cast<double2*>(ws + gn_counters_bytes(a->n) + gn_stats_bytes(a->n, a->groups));
+    p.partials = reinterpret_cast<float4*>(ws + gn_counters_bytes(a->n) + gn_stats_bytes(a->n, a->groups));
     p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
     p.sub = gn_sub_blocks(a->hw);
     p.eps = a->eps; p.act = a->act;
@@ -255,14 +320,15 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
     AB_REQUIRE(smem <= 48 * 1024, "channel count too large for the stats kernel");
     dim3 grid(p.sub, GN_SHARDS, a->n);
-    const long long total = static_cast<long long>(a->n) * a->hw * ncol;
-    int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148LL * 16));
+    const int apply_cols = ncol < GN_THREADS ? ncol : GN_THREADS;
+    const int apply_rows = (GN_THREADS / apply_cols) * GN_APPLY_ROWS;
+    dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
         gn_stats_kernel<__nv_bfloat16><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p);
+        gn_apply_kernel<__nv_bfloat16><<<blocks, GN_THREADS, 0, stream>>>(p);
     } else {
         gn_stats_kernel<__half><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__half><<<blocks, 256, 0, stream>>>(p);
+        gn_apply_kernel<__half><<<blocks, GN_THREADS, 0, stream>>>(p);
     }
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(2);
@@ -342,7 +408,7 @@ extern "C" int ab_groupnorm_static(const ab_groupnorm_args* a, void* stream_) {
     p.x = a->x; p.x2 = a->x2; p.y = a->y; p.gamma = a->gamma; p.beta = a->beta; p.scale = a->scale; p.shift = a->shift;
     p.counters = reinterpret_cast<unsigned int*>(ws);
     p.stats = reinterpret_cast<float2*>(ws + kStaticCountersBytes);
-    p.partials = reinterpret_cast<double2*>(ws + kStaticCountersBytes + kStaticStatsBytes);
+    p.partials = reinterpret_cast<float4*>(ws + kStaticCountersBytes + kStaticStatsBytes);
     p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
     p.sub = gn_sub_blocks(a->hw);
     p.eps = a->eps; p.act = a->act;
@@ -353,14 +419,15 @@ extern "C" int ab_groupnorm_static(const ab_groupnorm_args* a, void* stream_) {
     // the block tickets must start at zero whatever an earlier (possibly failed) call left behind
     AB_CHECK_CUDA(cudaMemsetAsync(ws, 0, kStaticCountersBytes, stream));
     dim3 grid(p.sub, GN_SHARDS, a->n);
-    const long long total = static_cast<long long>(a->n) * a->hw * ncol;
-    int blocks = static_cast<int>(std::min<long long>((total + 255) / 256, 148LL * 16));
+    const int apply_cols = ncol < GN_THREADS ? ncol : GN_THREADS;
+    const int apply_rows = (GN_THREADS / apply_cols) * GN_APPLY_ROWS;
+    dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
         gn_stats_kernel<__nv_bfloat16><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p);
+        gn_apply_kernel<__nv_bfloat16><<<blocks, GN_THREADS, 0, stream>>>(p);
     } else {
         gn_stats_kernel<__half><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__half><<<blocks, 256, 0, stream>>>(p);
+        gn_apply_kernel<__half><<<blocks, GN_THREADS, 0, stream>>>(p);
     }
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(2);

@@ -66,7 +66,8 @@ int ab_gemm(const ab_gemm_args* args, void* stream);
 size_t ab_gemm_workspace_bytes(const ab_gemm_args* args);
 
 /* ---- K1 small-channel direct conv (conv_in / conv_out, Cin or Cout < 64) ------------------------ */
-/* x [N,H,W,Cin] -> out [N,Ho,Wo,Cout], weight [Cout, KH, KW, Cin], pad = KH/2, stride 1 or 2. */
+/* x [N,H,W,Cin] -> out [N,Ho,Wo,Cout], pad = KH/2, stride 1 or 2. Weight layout by shape class:
+ * Cout <= 8 and Cin % 8 == 0: [Cout, KH, KW, Cin]; otherwise (Cin <= 16, Cout % 8 == 0): [KH, KW, Cin, Cout]. */
 int ab_conv_direct(const void* x, const void* w, const void* bias, void* out, int n, int h, int wd, int cin,
                    int cout, int ksize, int stride, int act, int dtype, void* stream);
 

@@ -1,0 +1,28 @@
+"""Tiny driver for ncu captures: a few GEMM / conv / attention / GroupNorm calls at UNet shapes."""
+import sys
+import torch
+sys.path.insert(0, ".")
+from arbius_b200 import ops
+what = sys.argv[1] if len(sys.argv) > 1 else "gemm"
+dt = torch.float16
+torch.manual_seed(0)
+if what == "gemm":
+    for (m, n, k, bn) in [(154, 768, 768, 32), (8192, 320, 320, 96), (512, 1280, 1280, 32)]:
+        x = torch.randn(m, k, device="cuda", dtype=dt); w = torch.randn(n, k, device="cuda", dtype=dt); b = torch.randn(n, device="cuda", dtype=dt)
+        for _ in range(3):
+            ops.gemm(x, w, b, block_n=bn, splitk=1)
+elif what == "conv":
+    for (b_, h, w_, ci, co, bn) in [(2, 64, 64, 320, 320, 160), (2, 32, 32, 640, 640, 160), (1, 256, 256, 256, 256, 160)]:
+        x = torch.randn(b_, h, w_, ci, device="cuda", dtype=dt); wt = torch.randn(co, 9 * ci, device="cuda", dtype=dt); b = torch.randn(co, device="cuda", dtype=dt)
+        for _ in range(3):
+            ops.conv3x3(x, wt, b, block_n=bn, splitk=1)
+elif what == "attn":
+    q = torch.randn(2, 4096, 8, 40, device="cuda", dtype=dt); k = torch.randn_like(q); v = torch.randn_like(q)
+    for _ in range(3):
+        ops.flash_attn(q, k, v)
+elif what == "gn":
+    x = torch.randn(2, 4096, 320, device="cuda", dtype=dt); g = torch.randn(320, device="cuda", dtype=dt)
+    for _ in range(3):
+        ops.groupnorm(x, g, g, 32, 1e-5, "silu")
+torch.cuda.synchronize()
+print("ok")

@@ -1,0 +1,141 @@
+"""Measure every GEMM / conv shape of the SD-1.5 task under each (block_n, splitk) and keep the fastest.
+
+Runs the real pipeline once with recording on to collect the shape keys, then times each shape inside a
+CUDA graph (16 back-to-back calls rotating over weight copies so weights come from HBM, as in the real
+step) for every legal configuration. Writes arbius_b200/ops/tuned_sm100.json (if --write) and a report.
+"""
+import argparse
+import json
+import sys
+from collections import Counter
+
+import torch
+
+sys.path.insert(0, ".")
+import arbius_b200.ops  # noqa: E402,F401
+from arbius_b200 import ops  # noqa: E402
+
+G = sys.modules["arbius_b200.ops.gemm"]
+BNS = [32, 64, 96, 128, 160, 256]
+SPLITS = [1, 2, 3, 4, 6, 8]
+REPS = 16
+
+
+def time_graph(fn, iters=5):
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        fn()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    g.replay()
+    torch.cuda.synchronize()
+    best = 1e9
+    for _ in range(iters):
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return best * 1e3 / REPS   # us per call
+
+
+def bench_key(key, dt=torch.float16):
+    parts = key.split(":")
+    kind = parts[0]
+    res = {}
+    if kind in ("lin", "geglu"):
+        m, n, k = int(parts[1]), int(parts[2]), int(parts[3])
+        wbytes = n * k * 2
+        ncopy = max(2, min(REPS, (300 << 20) // max(wbytes, 1)))
+        x = torch.randn(m, k, device="cuda", dtype=dt)
+        ws = [torch.randn(n, k, device="cuda", dtype=dt) / k ** 0.5 for _ in range(ncopy)]
+        b = torch.randn(n, device="cuda", dtype=dt)
+        kc = (k + 63) // 64
+        flops = 2.0 * m * n * k
+        for bn in BNS:
+            if kind == "geglu" and bn % 32:
+                continue
+            if bn > 64 and bn >= 2 * n:
+                continue
+            for sk in SPLITS:
+                if sk > 1 and (kc // sk < 4 or m * n * sk * 4 > (512 << 20)):
+                    continue
+                def fn():
+                    for i in range(REPS):
+                        ops.gemm(x, ws[i % ncopy], b, geglu=(kind == "geglu"), block_n=bn, splitk=sk)
+                try:
+                    res[(bn, sk)] = time_graph(fn)
+                except RuntimeError as e:
+                    res[(bn, sk)] = float("inf")
+    else:
+        bhw, n, c = parts[1], int(parts[2]), int(parts[3])
+        b_, h, w = (int(v) for v in bhw.split("x"))
+        wbytes = n * 9 * c * 2
+        ncopy = max(2, min(REPS, (300 << 20) // wbytes))
+        x = torch.randn(b_, h, w, c, device="cuda", dtype=dt)
+        ws = [torch.randn(n, 9 * c, device="cuda", dtype=dt) / (9 * c) ** 0.5 for _ in range(ncopy)]
+        bias = torch.randn(n, device="cuda", dtype=dt)
+        kc = 9 * c // 64
+        m = b_ * h * w
+        flops = 2.0 * m * n * 9 * c
+        for bn in BNS:
+            if bn > 64 and bn >= 2 * n:
+                continue
+            for sk in SPLITS:
+                if sk > 1 and (kc // sk < 4 or m * n * sk * 4 > (512 << 20)):
+                    continue
+                def fn():
+                    for i in range(REPS):
+                        ops.conv3x3(x, ws[i % ncopy], bias, block_n=bn, splitk=sk)
+                try:
+                    res[(bn, sk)] = time_graph(fn)
+                except RuntimeError:
+                    res[(bn, sk)] = float("inf")
+    return res, flops, wbytes
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--write", action="store_true")
+    ap.add_argument("--out", default="gpurun_out/tune_report.json")
+    ap.add_argument("--size", type=int, default=512)
+    a = ap.parse_args()
+    from arbius_b200.models.sd15.pipeline import SD15Config, SD15Pipeline
+    pipe = SD15Pipeline(SD15Config(), backend="native", device="cuda", dtype=torch.float16, use_graph=False)
+    G.RECORD = []
+    pipe.generate("cat", "", a.size, a.size, 2, 7.5, "DPMSolverMultistep", seed=1)
+    torch.cuda.synchronize()
+    counts = Counter(G.RECORD)
+    G.RECORD = None
+    del pipe
+    torch.cuda.empty_cache()
+    report, table = [], {}
+    for key, cnt in sorted(counts.items(), key=lambda kv: -kv[1]):
+        res, flops, wbytes = bench_key(key)
+        (bn, sk), us = min(res.items(), key=lambda kv: kv[1])
+        parts = key.split(":")
+        if parts[0] == "conv":
+            b_, h, w = (int(v) for v in parts[1].split("x"))
+            m, n, kc = b_ * h * w, int(parts[2]), 9 * int(parts[3]) // 64
+        else:
+            m, n, kc = int(parts[1]), int(parts[2]), (int(parts[3]) + 63) // 64
+        cur_sk = G.auto_splitk(m, n, kc)
+        cur = min((v for (b2, s2), v in res.items() if s2 == cur_sk), default=float("nan"))
+        table[key] = [bn, sk]
+        report.append(dict(key=key, calls_per_2steps=cnt, best=[bn, sk], us=round(us, 2),
+                           tflops=round(flops / us / 1e6, 1), w_gbs=round(wbytes / us / 1e3, 1),
+                           heuristic_splitk=cur_sk, heuristic_best_us=round(cur, 2),
+                           all={f"{b2}/{s2}": round(v, 2) for (b2, s2), v in sorted(res.items())}))
+        print(json.dumps({k: v for k, v in report[-1].items() if k != "all"}), flush=True)
+    json.dump(report, open(a.out, "w"), indent=1)
+    if a.write:
+        json.dump(table, open("gpurun_out/tuned_sm100.json", "w"), indent=0, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()
