@@ -277,6 +277,8 @@ flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
+#include "attention_v2.cuh"
+
 template <int NCH, typename T>
 static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                        cudaStream_t stream) {
@@ -324,7 +326,7 @@ extern "C" int ab_flash_attn(const ab_attn_args* a, void* stream_) {
     if (mk(&tk, a->k, a->lk, a->k_bs, a->k_ls)) return -1;
     if (mk(&tv, a->v, a->lk, a->v_bs, a->v_ls)) return -1;
 #define AB_ATT(T)                                                      \
-    (nch == 1 ? launch_attn<1, T>(tq, tk, tv, p, stream)               \
+    (nch == 1 ? (a->lq > 128 ? launch_attn2<T>(tq, tk, tv, p, stream) : launch_attn<1, T>(tq, tk, tv, p, stream)) \
      : nch == 2 ? launch_attn<2, T>(tq, tk, tv, p, stream)             \
                 : launch_attn<3, T>(tq, tk, tv, p, stream))
     return a->dtype == AB_BF16 ? AB_ATT(__nv_bfloat16) : AB_ATT(__half);

@@ -1,0 +1,284 @@
+// Flash attention v2 for head_dim <= 64: two 128-row query tiles per CTA, ping-ponged (FA4-style).
+// Included by attention.cu inside namespace ab, after AttnParams.
+//
+//   warp 0        TMA: Q_A, Q_B once; K_j/V_j ring (3 stages)
+//   warp 1        MMA issuer: QK_A, QK_B, then per KV tile  PV_A, QK_A(next), PV_B, QK_B(next)
+//   warps 2..5    softmax for tile A (TMEM lane quarters 2,3,0,1)
+//   warps 6..9    softmax for tile B
+// While one tile's softmax runs on the MUFU/FMA pipes the tensor core works on the other tile, and
+// K/V shared-memory traffic is halved (both query tiles consume the same stage).
+// TMEM: S_A [0,128) S_B [128,256) O_A [256,320) O_B [320,384).
+
+constexpr int A2_THREADS = 320;
+constexpr int A2_STAGES = 3;
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(A2_THREADS, 1)
+flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                   const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+    constexpr float kRescaleThreshold = 8.0f;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;                                   // 2 x 16 KB
+    uint8_t* sK = sQ + 2 * CHUNK_BYTES;                   // STAGES x 16 KB
+    uint8_t* sV = sK + A2_STAGES * CHUNK_BYTES;           // STAGES x 16 KB
+    uint8_t* sP = sV + A2_STAGES * CHUNK_BYTES;           // 2 tiles x 32 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 4 * CHUNK_BYTES);
+    uint64_t* q_full = bars;                  // 1
+    uint64_t* kv_full = bars + 1;             // STAGES
+    uint64_t* kv_empty = kv_full + A2_STAGES; // STAGES
+    uint64_t* s_full = kv_empty + A2_STAGES;  // 2
+    uint64_t* p_full = s_full + 2;            // 2
+    uint64_t* o_full = p_full + 2;            // 2
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * 256;
+    const int h = blockIdx.y;
+    const int b = blockIdx.z;
+    const int D = p.head_dim;
+    const int DP = (D + 15) & ~15;
+    const bool b_active = q0 + 128 < p.lq;
+    int kv_len = p.lk;
+    if (p.causal) kv_len = min(p.lk, q0 + 256);
+    const int NT = (kv_len + ATT_BN - 1) / ATT_BN;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < A2_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+        for (int t = 0; t < 2; ++t) { mbar_init(&s_full[t], 1); mbar_init(&p_full[t], 128); mbar_init(&o_full[t], 1); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(q_full, (b_active ? 2 : 1) * CHUNK_BYTES);
+            tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
+            if (b_active) tma_load_4d(sQ + CHUNK_BYTES, &tmQ, q_full, 0, h, q0 + 128, b);
+            int stage = 0; uint32_t phase = 0;
+            for (int j = 0; j < NT; ++j) {
+                mbar_wait(&kv_empty[stage], phase ^ 1);
+                mbar_expect_tx(&kv_full[stage], 2 * CHUNK_BYTES);
+                tma_load_4d(sK + stage * CHUNK_BYTES, &tmK, &kv_full[stage], 0, h, j * ATT_BN, b);
+                tma_load_4d(sV + stage * CHUNK_BYTES, &tmV, &kv_full[stage], 0, h, j * ATT_BN, b);
+                if (++stage == A2_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc_qk = make_idesc_f16(ATT_BM, ATT_BN, DT<T>::kBf16, false, false);
+            const uint32_t idesc_pv = make_idesc_f16(ATT_BM, DP, DT<T>::kBf16, false, true);
+            auto issue_qk = [&](int t, int j) {
+                const uint32_t q_addr = smem_u32(sQ + t * CHUNK_BYTES);
+                const uint32_t k_addr = smem_u32(sK + (j % A2_STAGES) * CHUNK_BYTES);
+                for (int ks = 0; ks < DP / 16; ++ks)
+                    umma_ss(tmem_base + static_cast<uint32_t>(t) * 128u, make_smem_desc(q_addr + ks * 32, 16, 1024, kSwizzle128),
+                            make_smem_desc(k_addr + ks * 32, 16, 1024, kSwizzle128), idesc_qk, ks > 0 ? 1u : 0u);
+                umma_commit(&s_full[t]);
+            };
+            auto issue_pv = [&](int t, int j) {
+                mbar_wait(&p_full[t], j & 1);
+                tc_fence_after();
+                const uint32_t p_addr = smem_u32(sP + t * 2 * CHUNK_BYTES);
+                const uint32_t v_addr = smem_u32(sV + (j % A2_STAGES) * CHUNK_BYTES);
+                for (int ks = 0; ks < ATT_BN / 16; ++ks)
+                    umma_ss(tmem_base + 256u + static_cast<uint32_t>(t) * 64u,
+                            make_smem_desc(p_addr + (ks >> 2) * CHUNK_BYTES + (ks & 3) * 32, 16, 1024, kSwizzle128),
+                            make_smem_desc(v_addr + ks * 16 * 128, CHUNK_BYTES, 1024, kSwizzle128), idesc_pv,
+                            (j > 0 || ks > 0) ? 1u : 0u);
+                umma_commit(&o_full[t]);
+            };
+            mbar_wait(q_full, 0);
+            mbar_wait(&kv_full[0], 0);
+            tc_fence_after();
+            issue_qk(0, 0);
+            if (b_active) issue_qk(1, 0);
+            for (int j = 0; j < NT; ++j) {
+                const bool more = j + 1 < NT;
+                if (more) {
+                    mbar_wait(&kv_full[(j + 1) % A2_STAGES], ((j + 1) / A2_STAGES) & 1);
+                    tc_fence_after();
+                }
+                issue_pv(0, j);
+                if (more) issue_qk(0, j + 1);
+                if (b_active) {
+                    issue_pv(1, j);
+                    if (more) issue_qk(1, j + 1);
+                }
+                // every MMA that read stage j has been issued; this commit fires when they are all done.
+                // QK(j+1) issued above read stage j+1, which only delays the release slightly.
+                umma_commit(&kv_empty[j % A2_STAGES]);
+            }
+        }
+    } else {
+        // ================= softmax warps: tile t, one thread per query row =================
+        const int t = (warp - 2) >> 2;
+        const int qd = warp & 3;
+        const int r = qd * 32 + lane;
+        const int qrow = q0 + t * 128 + r;
+        const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
+        const bool active = (t == 0) || b_active;
+        float m_ref = -INFINITY;
+        float l_sum = 0.f;
+        uint8_t* pbuf = sP + t * 2 * CHUNK_BYTES;
+        const uint32_t s_addr = tmem_base + lane_off + static_cast<uint32_t>(t) * 128u;
+        const uint32_t o_addr = tmem_base + lane_off + 256u + static_cast<uint32_t>(t) * 64u;
+        if (active) {
+            for (int j = 0; j < NT; ++j) {
+                mbar_wait(&s_full[t], j & 1);
+                tc_fence_after();
+                const int col0 = j * ATT_BN;
+                int col_hi = p.lk;
+                if (p.causal) col_hi = min(col_hi, qrow + 1);
+                const bool full_tile = __all_sync(0xffffffffu, col0 + ATT_BN <= col_hi);
+                // ---- pass 1: raw row max ----
+                float mx = -INFINITY;
+#pragma unroll 1
+                for (int c = 0; c < ATT_BN / 32; ++c) {
+                    uint32_t raw[32];
+                    tmem_ld32(s_addr + c * 32, raw);
+                    tmem_wait_ld();
+                    if (full_tile) {
+                        float m0 = mx, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            m0 = fmaxf(m0, __uint_as_float(raw[i]));
+                            m1 = fmaxf(m1, __uint_as_float(raw[i + 1]));
+                            m2 = fmaxf(m2, __uint_as_float(raw[i + 2]));
+                            m3 = fmaxf(m3, __uint_as_float(raw[i + 3]));
+                        }
+                        mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (col0 + c * 32 + i < col_hi) mx = fmaxf(mx, __uint_as_float(raw[i]));
+                    }
+                }
+                mx *= p.scale_log2;                     // scale > 0: max commutes with the scaling
+                bool need = false;
+                float factor = 1.f;
+                if (mx > m_ref + kRescaleThreshold || m_ref == -INFINITY) {
+                    if (mx != -INFINITY) {
+                        need = (m_ref != -INFINITY);
+                        factor = need ? exp2f(m_ref - mx) : 1.f;
+                        m_ref = mx;
+                    }
+                }
+                const bool warp_need = __any_sync(0xffffffffu, need);
+                if (j > 0) {
+                    mbar_wait(&o_full[t], (j - 1) & 1);      // PV(j-1) done: O stable, P buffer free
+                    tc_fence_after();
+                }
+                if (warp_need) {
+                    l_sum *= factor;
+#pragma unroll 1
+                    for (int c = 0; c < DP; c += 16) {
+                        uint32_t raw[16];
+                        tmem_ld16(o_addr + c, raw);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) raw[i] = __float_as_uint(__uint_as_float(raw[i]) * factor);
+                        asm volatile(
+                            "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, "
+                            "%11, %12, %13, %14, %15, %16};\n" ::"r"(o_addr + c),
+                            "r"(raw[0]), "r"(raw[1]), "r"(raw[2]), "r"(raw[3]), "r"(raw[4]), "r"(raw[5]), "r"(raw[6]),
+                            "r"(raw[7]), "r"(raw[8]), "r"(raw[9]), "r"(raw[10]), "r"(raw[11]), "r"(raw[12]),
+                            "r"(raw[13]), "r"(raw[14]), "r"(raw[15])
+                            : "memory");
+                    }
+                    tmem_wait_st();
+                }
+                // ---- pass 2: p = 2^(s*c - m), row sum, P -> smem (K-major, 128-byte swizzle) ----
+                const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+                float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+#pragma unroll 1
+                for (int c = 0; c < ATT_BN / 32; ++c) {
+                    uint32_t raw[32];
+                    tmem_ld32(s_addr + c * 32, raw);
+                    tmem_wait_ld();
+                    float pv[32];
+                    if (full_tile) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) pv[i] = ex2_approx(fmaf(__uint_as_float(raw[i]), p.scale_log2, neg_m));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            pv[i] = (col0 + c * 32 + i < col_hi)
+                                        ? ex2_approx(fmaf(__uint_as_float(raw[i]), p.scale_log2, neg_m)) : 0.f;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) { sum0 += pv[i]; sum1 += pv[i + 1]; sum2 += pv[i + 2]; sum3 += pv[i + 3]; }
+                    uint8_t* slab = pbuf + (c >> 1) * CHUNK_BYTES + r * 128;
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        float f8[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) f8[i] = pv[8 * g + i];
+                        const int chunk16 = (c & 1) * 4 + g;
+                        *reinterpret_cast<uint4*>(slab + ((chunk16 ^ (r & 7)) << 4)) = pack8<T>(f8);
+                    }
+                }
+                l_sum += (sum0 + sum1) + (sum2 + sum3);
+                fence_proxy_async();
+                tc_fence_before();
+                mbar_arrive(&p_full[t]);
+            }
+            // ---- epilogue ----
+            mbar_wait(&o_full[t], (NT - 1) & 1);
+            tc_fence_after();
+            const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
+            T* orow = reinterpret_cast<T*>(p.out) + static_cast<long long>(b) * p.o_bs +
+                      static_cast<long long>(qrow) * p.o_ls + static_cast<long long>(h) * D;
+#pragma unroll 1
+            for (int c = 0; c < DP; c += 16) {
+                uint32_t raw[16];
+                tmem_ld16(o_addr + c, raw);
+                tmem_wait_ld();
+                if (qrow < p.lq) {
+#pragma unroll
+                    for (int g = 0; g < 2; ++g) {
+                        if (c + 8 * g < D) {
+                            float f8[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) f8[i] = __uint_as_float(raw[8 * g + i]) * inv;
+                            *reinterpret_cast<uint4*>(orow + c + 8 * g) = pack8<T>(f8);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+template <typename T>
+static int launch_attn2(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
+                        cudaStream_t stream) {
+    constexpr int smem = (2 + 2 * A2_STAGES + 4) * CHUNK_BYTES + 16 * 8 + 16 + 1024;
+    static bool configured = false;
+    if (!configured) {
+        AB_CHECK_CUDA(cudaFuncSetAttribute(flash_attn2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+    }
+    dim3 grid((p.lq + 255) / 256, p.heads, p.batch);
+    flash_attn2_kernel<T><<<grid, A2_THREADS, smem, stream>>>(tq, tk, tv, p);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

@@ -11,7 +11,7 @@ objs=()
 for src in "$here"/*.cu; do
   obj="$out/obj/$(basename "${src%.cu}").o"
   objs+=("$obj")
-  if [[ ! -f "$obj" || "$src" -nt "$obj" || "$here/common.cuh" -nt "$obj" || "$here/../include/arbius_b200.h" -nt "$obj" ]]; then
+  if [[ ! -f "$obj" || "$src" -nt "$obj" || -n "$(find "$here" -name "*.cuh" -newer "$obj")" || "$here/../include/arbius_b200.h" -nt "$obj" ]]; then
     "$NVCC" "${FLAGS[@]}" -Xptxas -v -c "$src" -o "$obj" 2> "$obj.log" &
     pids+=($!)
   fi
