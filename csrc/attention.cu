@@ -35,6 +35,7 @@ struct AttnParams {
     long long o_bs, o_ls;
     float scale_log2;   // softmax scale * log2(e)
     int causal;
+    int tiles_per_src;  // multi-source K/V: 128-key tiles held by each source (patch-parallel ranks)
 };
 
 template <int NCH, typename T>
@@ -331,4 +332,53 @@ extern "C" int ab_flash_attn(const ab_attn_args* a, void* stream_) {
                 : launch_attn<3, T>(tq, tk, tv, p, stream))
     return a->dtype == AB_BF16 ? AB_ATT(__nv_bfloat16) : AB_ATT(__half);
 #undef AB_ATT
+}
+
+// ---- patch-parallel attention: K/V spread over the GPUs of a subset, gathered by the kernel's own TMA loads ----
+// k_ptrs[s] / v_ptrs[s] are the (local or peer-mapped) [B, lk_per_src, H, D] buffers of source s, all with the
+// same strides; the global key order is source 0's keys, then source 1's, ...  See include/arbius_b200.h.
+extern "C" int ab_flash_attn_multi(const ab_attn_args* a, const void* const* k_ptrs, const void* const* v_ptrs,
+                                   int nsrc, int lk_per_src, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && a->q && a->out && k_ptrs && v_ptrs, "null pointer");
+    AB_REQUIRE(nsrc == 1 || nsrc == 2 || nsrc == 4 || nsrc == 8, "nsrc must be 1, 2, 4 or 8");
+    AB_REQUIRE(a->head_dim % 8 == 0 && a->head_dim >= 16 && a->head_dim <= 64, "multi-source attention needs head_dim in [16,64]");
+    AB_REQUIRE(lk_per_src > 0 && lk_per_src % ATT_BN == 0, "keys per source must be a multiple of 128");
+    AB_REQUIRE(!a->causal, "causal masking is not supported in the multi-source path");
+    const int D = a->head_dim;
+    AttnParams p{};
+    p.out = a->out; p.batch = a->batch; p.heads = a->heads; p.lq = a->lq; p.lk = nsrc * lk_per_src; p.head_dim = D;
+    p.o_bs = a->o_bs; p.o_ls = a->o_ls;
+    const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
+    p.scale_log2 = scale * 1.4426950408889634f;
+    p.causal = 0;
+    p.tiles_per_src = lk_per_src / ATT_BN;
+    auto mk = [&](CUtensorMap* tm, const void* base, int L, long long bs, long long ls) {
+        uint64_t dims[4] = {(uint64_t)D, (uint64_t)a->heads, (uint64_t)L, (uint64_t)a->batch};
+        uint64_t str[3] = {(uint64_t)D * 2, (uint64_t)ls * 2, (uint64_t)(a->batch > 1 ? bs : ls * L) * 2};
+        uint32_t box[4] = {64, 1, 128, 1};
+        return ab_make_tensor_map(tm, a->dtype, 4, base, dims, str, box, 128);
+    };
+    CUtensorMap tq;
+    if (mk(&tq, a->q, a->lq, a->q_bs, a->q_ls)) return -1;
+#define AB_ATT_MULTI(T, N)                                                                   \
+    {                                                                                         \
+        KvMaps<N> kv;                                                                         \
+        for (int s = 0; s < N; ++s) {                                                         \
+            if (mk(&kv.k[s], k_ptrs[s], lk_per_src, a->k_bs, a->k_ls)) return -1;             \
+            if (mk(&kv.v[s], v_ptrs[s], lk_per_src, a->v_bs, a->v_ls)) return -1;             \
+        }                                                                                     \
+        return launch_attn2_multi<T, N>(tq, kv, p, stream);                                   \
+    }
+#define AB_ATT_MULTI_T(T)                                  \
+    switch (nsrc) {                                        \
+        case 1: AB_ATT_MULTI(T, 1)                         \
+        case 2: AB_ATT_MULTI(T, 2)                         \
+        case 4: AB_ATT_MULTI(T, 4)                         \
+        default: AB_ATT_MULTI(T, 8)                        \
+    }
+    if (a->dtype == AB_BF16) { AB_ATT_MULTI_T(__nv_bfloat16) } else { AB_ATT_MULTI_T(__half) }
+#undef AB_ATT_MULTI_T
+#undef AB_ATT_MULTI
 }

@@ -18,10 +18,19 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
-template <typename T>
+// K/V may live in up to NSRC buffers (one per GPU of a patch-parallel subset, peer-mapped over NVLink):
+// KV tile j comes from source j / tiles_per_src. The tile ORDER is global and fixed, so the result is
+// bit-identical however the keys are spread over GPUs — the all-gather is the TMA loads themselves.
+template <int NSRC>
+struct KvMaps {
+    CUtensorMap k[NSRC];
+    CUtensorMap v[NSRC];
+};
+
+template <typename T, int NSRC>
 __global__ void __launch_bounds__(A2_THREADS, 1)
-flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                   const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ KvMaps<NSRC> kv,
+                   const AttnParams p) {
     constexpr float kRescaleThreshold = 8.0f;
 
     extern __shared__ uint8_t smem_raw[];
@@ -52,7 +61,8 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int NT = (kv_len + ATT_BN - 1) / ATT_BN;
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(&tmQ);
+        for (int s = 0; s < NSRC; ++s) { tma_prefetch_desc(&kv.k[s]); tma_prefetch_desc(&kv.v[s]); }
         mbar_init(q_full, 1);
         for (int s = 0; s < A2_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
         for (int t = 0; t < 2; ++t) { mbar_init(&s_full[t], 1); mbar_init(&p_full[t], 128); mbar_init(&o_full[t], 1); }
@@ -73,8 +83,10 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             for (int j = 0; j < NT; ++j) {
                 mbar_wait(&kv_empty[stage], phase ^ 1);
                 mbar_expect_tx(&kv_full[stage], 2 * CHUNK_BYTES);
-                tma_load_4d(sK + stage * CHUNK_BYTES, &tmK, &kv_full[stage], 0, h, j * ATT_BN, b);
-                tma_load_4d(sV + stage * CHUNK_BYTES, &tmV, &kv_full[stage], 0, h, j * ATT_BN, b);
+                int src = 0, row = j * ATT_BN;
+                if (NSRC > 1) { src = j / p.tiles_per_src; row = (j - src * p.tiles_per_src) * ATT_BN; }
+                tma_load_4d(sK + stage * CHUNK_BYTES, &kv.k[src], &kv_full[stage], 0, h, row, b);
+                tma_load_4d(sV + stage * CHUNK_BYTES, &kv.v[src], &kv_full[stage], 0, h, row, b);
                 if (++stage == A2_STAGES) { stage = 0; phase ^= 1; }
             }
         }
@@ -267,18 +279,26 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
-template <typename T>
-static int launch_attn2(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
-                        cudaStream_t stream) {
+template <typename T, int NSRC>
+static int launch_attn2_multi(const CUtensorMap& tq, const KvMaps<NSRC>& kv, const AttnParams& p, cudaStream_t stream) {
     constexpr int smem = (2 + 2 * A2_STAGES + 4) * CHUNK_BYTES + 16 * 8 + 16 + 1024;
     static bool configured = false;
     if (!configured) {
-        AB_CHECK_CUDA(cudaFuncSetAttribute(flash_attn2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        AB_CHECK_CUDA(cudaFuncSetAttribute(flash_attn2_kernel<T, NSRC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
     dim3 grid((p.lq + 255) / 256, p.heads, p.batch);
-    flash_attn2_kernel<T><<<grid, A2_THREADS, smem, stream>>>(tq, tk, tv, p);
+    flash_attn2_kernel<T, NSRC><<<grid, A2_THREADS, smem, stream>>>(tq, kv, p);
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(1);
     return 0;
+}
+
+template <typename T>
+static int launch_attn2(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
+                        cudaStream_t stream) {
+    KvMaps<1> kv;
+    kv.k[0] = tk;
+    kv.v[0] = tv;
+    return launch_attn2_multi<T, 1>(tq, kv, p, stream);
 }

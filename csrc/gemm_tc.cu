@@ -47,6 +47,15 @@ struct GemmParams {
     float out_scale;
     int splitk, chunks_per_split;
     int ldo, ldr, ldrb;
+    // ---- multi-GPU extensions (one NVSwitch box; pointers may be peer-mapped) ----
+    // all-gather -> GEMM: rows of A live in `nsrc` buffers of `tiles_per_src` 128-row tiles each; the gather is
+    // the TMA loads themselves (linear mode only).
+    int nsrc, tiles_per_src;
+    // GEMM -> reduce-scatter: the fp32 partial tile of split (z_base + blockIdx.z) for output row m goes to the
+    // workspace of the rank that owns m; owners then sum the 8 canonical K shards in order.
+    int rows_per_owner, z_base;
+    float* ws_peer[8];
+    alignas(64) CUtensorMap amaps[8];
 };
 
 template <typename T>
@@ -143,7 +152,7 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
 template <int BN, int STAGES, typename T, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
-               const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+               const __grid_constant__ CUtensorMap tmB, const __grid_constant__ GemmParams p) {
     constexpr int A_BYTES = BM * BK * 2;
     constexpr int B_BYTES = BN * BK * 2;
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -221,7 +230,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const int dh = tap / 3 - 1, dw = tap % 3 - 1;
                     tma_load_4d(sa, ma, &full_bar[stage], c0, w0 + dw, h0 + dh, i0);
                 } else {
-                    tma_load_2d(sa, ma, &full_bar[stage], c0, m0);
+                    if (p.nsrc > 1) {
+                        const int src = tile_m / p.tiles_per_src;
+                        tma_load_2d(sa, &p.amaps[src], &full_bar[stage], c0, (tile_m - src * p.tiles_per_src) * BM);
+                    } else {
+                        tma_load_2d(sa, ma, &full_bar[stage], c0, m0);
+                    }
                 }
                 tma_load_2d(sb, &tmB, &full_bar[stage], kc * BK, n0);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -310,7 +324,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
                 if (p.splitk > 1) {
-                    float* ws = p.workspace + (static_cast<long long>(blockIdx.z) * p.M + out_row) * p.N + n_base;
+                    const int owner = static_cast<int>(out_row / p.rows_per_owner);
+                    float* ws = p.ws_peer[owner] + (static_cast<long long>(p.z_base + blockIdx.z) * p.rows_per_owner +
+                                                    (out_row - static_cast<long long>(owner) * p.rows_per_owner)) * p.N + n_base;
 #pragma unroll
                     for (int g = 0; g < 8; ++g)
                         if (n_base + 4 * g < p.N)
@@ -478,10 +494,14 @@ extern "C" size_t ab_gemm_workspace_bytes(const ab_gemm_args* a) {
     return static_cast<size_t>(a->splitk) * a->M * a->N * sizeof(float);
 }
 
-extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
+extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) { return ab_gemm_dist(a, nullptr, 0, stream_); }
+
+extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, int phase, void* stream_) {
     using namespace ab;
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-    AB_REQUIRE(a && a->a && a->w && a->out, "null pointer");
+    const bool ag = d && d->nsrc > 1;
+    const bool rs = d && d->rs_world >= 1;
+    AB_REQUIRE(a && (a->a || ag) && a->w && a->out, "null pointer");
     AB_REQUIRE(a->M > 0 && a->N > 0 && a->K1 > 0, "bad shape");
     AB_REQUIRE(a->N % 8 == 0, "N must be a multiple of 8");
     const int Ktot = a->K1 + a->K2;
@@ -525,7 +545,41 @@ extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
     p.chunks_per_split = (total_chunks + splitk - 1) / splitk;
     splitk = (total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;   // no empty splits
     p.splitk = splitk;
-    if (splitk > 1) AB_REQUIRE(a->workspace, "split-K needs a workspace");
+    int grid_z = splitk;
+    p.rows_per_owner = a->M; p.z_base = 0; p.ws_peer[0] = p.workspace;
+    if (rs) {
+        // canonical 8 K shards; this rank computes 8 / rs_world of them over its local K slice
+        AB_REQUIRE(!a->conv && (d->rs_world == 1 || d->rs_world == 2 || d->rs_world == 4 || d->rs_world == 8),
+                   "reduce-scatter mode: linear GEMM, 1/2/4/8 ranks");
+        AB_REQUIRE(a->M % d->rs_world == 0, "reduce-scatter: M must divide evenly over the ranks");
+        grid_z = 8 / d->rs_world;
+        // shard boundaries must be the same K offsets for every rank count: global K % 512 == 0
+        AB_REQUIRE(total_chunks % grid_z == 0 && Ktot % BK == 0,
+                   "reduce-scatter: global K must be a multiple of 512 (8 canonical shards of whole 64-wide chunks)");
+        p.chunks_per_split = total_chunks / grid_z;
+        p.splitk = splitk = 8;
+        p.rows_per_owner = a->M / d->rs_world;
+        p.z_base = d->rs_rank * grid_z;
+        for (int r = 0; r < d->rs_world; ++r) {
+            AB_REQUIRE(d->ws_peers[r], "reduce-scatter: missing workspace pointer");
+            p.ws_peer[r] = reinterpret_cast<float*>(d->ws_peers[r]);
+        }
+        p.workspace = p.ws_peer[d->rs_rank];
+    }
+    if (splitk > 1) AB_REQUIRE(p.workspace, "split-K needs a workspace");
+    if (ag) {
+        AB_REQUIRE(!a->conv && a->K2 == 0, "all-gather mode: linear GEMM without virtual concat");
+        AB_REQUIRE(d->nsrc == 2 || d->nsrc == 4 || d->nsrc == 8, "all-gather mode: 2/4/8 sources");
+        AB_REQUIRE(d->rows_per_src % BM == 0 && a->M == d->nsrc * d->rows_per_src, "all-gather mode: rows per source must be a multiple of 128");
+        p.nsrc = d->nsrc;
+        p.tiles_per_src = d->rows_per_src / BM;
+        for (int s = 0; s < d->nsrc; ++s) {
+            uint64_t dims[2] = {(uint64_t)a->K1, (uint64_t)d->rows_per_src};
+            uint64_t str[1] = {(uint64_t)a->K1 * 2};
+            uint32_t box[2] = {BK, BM};
+            if (ab_make_tensor_map(&p.amaps[s], a->dtype, 2, d->a_srcs[s], dims, str, box, 128)) return -1;
+        }
+    }
 
     int bn = a->block_n > 0 ? a->block_n : auto_block_n(tiles_m * splitk, a->N, a->geglu != 0);
 
@@ -547,7 +601,8 @@ extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
         uint64_t dims[2] = {(uint64_t)a->K1, (uint64_t)a->M};
         uint64_t str[1] = {(uint64_t)a->K1 * esz};
         uint32_t box[2] = {BK, BM};
-        if (ab_make_tensor_map(&tmA, a->dtype, 2, a->a, dims, str, box, 128)) return -1;
+        if (ag) tmA = p.amaps[0];
+        else if (ab_make_tensor_map(&tmA, a->dtype, 2, a->a, dims, str, box, 128)) return -1;
         tmA2 = tmA;
         if (a->K2 > 0) {
             uint64_t dims2[2] = {(uint64_t)a->K2, (uint64_t)a->M};
@@ -563,14 +618,15 @@ extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
         if (ab_make_tensor_map(&tmB, a->dtype, 2, a->w, dims, str, box, 128)) return -1;
     }
 
-    dim3 grid(tiles_m, (a->N + bn - 1) / bn, splitk);
+    dim3 grid(tiles_m, (a->N + bn - 1) / bn, grid_z);
     int epi = a->geglu ? EPI_GEGLU
             : a->act == ACT_NONE ? EPI_NONE
             : a->act == ACT_SILU ? EPI_SILU
             : a->act == ACT_GELU ? EPI_GELU
             : a->act == ACT_QUICK_GELU ? EPI_QGELU : EPI_ANY;
     const int main_epi = splitk > 1 ? EPI_NONE : epi;     // with split-K the main kernel only stores fp32 partials
-    int rc;
+    int rc = 0;
+    if (phase != 2) {
 #define AB_GEMM_EPI(T)                                                                                     \
     switch (main_epi) {                                                                                    \
         case EPI_NONE: rc = dispatch_bn<T, EPI_NONE>(bn, tmA, tmA2, tmB, p, grid, stream); break;          \
@@ -582,8 +638,10 @@ extern "C" int ab_gemm(const ab_gemm_args* a, void* stream_) {
     }
     if (a->dtype == AB_BF16) { AB_GEMM_EPI(__nv_bfloat16) } else { AB_GEMM_EPI(__half) }
 #undef AB_GEMM_EPI
+    }
     if (rc) return rc;
-    if (splitk > 1) {
+    if (splitk > 1 && phase != 1) {
+        if (rs) { p.M = p.rows_per_owner; p.splitk = 8; }      // owners reduce their own row band
         // one thread per (row, 32-column chunk); 64-thread blocks keep many CTAs in flight for small M*N
         const long long work = static_cast<long long>(p.M) * ((p.N + 31) / 32);
         const int threads = 64;

@@ -1,0 +1,70 @@
+// Peer-memory runtime for one NVSwitch box: a per-rank heap that every GPU of a subset maps into its own
+// address space (CUDA IPC), and a device-side barrier over peer-mapped flags. SURVEY §5.9 / §8 row R1.
+// Kernels then address remote tiles directly (TMA or ld/st through the peer mapping); no host round trip and no
+// NCCL call sits between a compute step and the data it needs from another GPU.
+#include <stdio.h>
+
+#include "../include/arbius_b200.h"
+#include "common.cuh"
+
+extern "C" void ab_count_launch(int n);
+
+// Heap memory comes straight from cudaMalloc (IPC handles cover whole allocations).
+extern "C" int ab_heap_alloc(void** ptr, size_t bytes) {
+    AB_REQUIRE(ptr && bytes > 0, "bad arguments");
+    AB_CHECK_CUDA(cudaMalloc(ptr, bytes));
+    AB_CHECK_CUDA(cudaMemset(*ptr, 0, bytes));
+    return 0;
+}
+extern "C" int ab_heap_free(void* ptr) {
+    AB_CHECK_CUDA(cudaFree(ptr));
+    return 0;
+}
+extern "C" int ab_ipc_get_handle(void* ptr, unsigned char* handle64) {
+    cudaIpcMemHandle_t h;
+    AB_CHECK_CUDA(cudaIpcGetMemHandle(&h, ptr));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle64, &h, 64);
+    return 0;
+}
+extern "C" int ab_ipc_open_handle(const unsigned char* handle64, void** ptr) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    AB_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int ab_ipc_close_handle(void* ptr) {
+    AB_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+    return 0;
+}
+
+namespace ab {
+struct PeerFlags { unsigned int* flags[8]; };   // flags[r] = rank r's flag array (peer-mapped), [8] slots each
+
+// Rank `rank` publishes `epoch` into slot [rank] of every peer's flag array, then waits until every peer has
+// published the same epoch into its own array. System-scope release/acquire orders the data written before.
+__global__ void peer_barrier_kernel(PeerFlags f, int rank, int world, unsigned int epoch) {
+    const int t = threadIdx.x;
+    if (t < world) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.flags[t] + rank), "r"(epoch) : "memory");
+        long long t0 = clock64();
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f.flags[rank] + t) : "memory");
+            if (clock64() - t0 > 20000000000LL) { printf("peer barrier timeout rank %d waiting for %d\n", rank, t); __trap(); }
+        } while (static_cast<int>(v - epoch) < 0);
+    }
+}
+}  // namespace ab
+
+extern "C" int ab_peer_barrier(void* const* flag_ptrs, int rank, int world, unsigned int epoch, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(flag_ptrs && world >= 1 && world <= 8 && rank >= 0 && rank < world, "bad arguments");
+    ab::PeerFlags f{};
+    for (int r = 0; r < world; ++r) f.flags[r] = reinterpret_cast<unsigned int*>(flag_ptrs[r]);
+    ab::peer_barrier_kernel<<<1, 32, 0, stream>>>(f, rank, world, epoch);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

@@ -63,6 +63,21 @@ typedef struct {
   int ldrb;                 /* rowbias row stride in elements, 0 = N */
 } ab_gemm_args;
 int ab_gemm(const ab_gemm_args* args, void* stream);
+/* Multi-GPU forms of the same kernel (one NVSwitch box; pointers may be peer-mapped addresses).
+ *   all-gather -> GEMM:  nsrc > 1: the rows of A live in nsrc buffers of rows_per_src rows each (args->a is
+ *                        ignored, M = nsrc*rows_per_src); tiles are fetched by TMA from whichever GPU owns them.
+ *   GEMM -> reduce-scatter: rs_world >= 1: K is cut into 8 canonical shards, this rank (rs_rank) computes
+ *                        8/rs_world of them over its local K slice and stores each fp32 partial row into the
+ *                        workspace of the rank that owns the row (ws_peers[owner], >= 8*(M/rs_world)*N*4 bytes).
+ *                        phase 1 = partials only; (peer barrier); phase 2 = owners sum shards 0..7 in order and
+ *                        apply the epilogue to their M/rs_world rows (args->out / residual are that local band).
+ *                        phase 0 = both (rs_world == 1). Results are bit-identical for rs_world in {1,2,4,8}.
+ * No counterpart in the reference (single GPU, no collectives: SURVEY section 2.8).                         */
+typedef struct {
+  const void* a_srcs[8]; int nsrc; int rows_per_src;
+  void* ws_peers[8]; int rs_world; int rs_rank;
+} ab_gemm_dist_args;
+int ab_gemm_dist(const ab_gemm_args* args, const ab_gemm_dist_args* dist, int phase, void* stream);
 size_t ab_gemm_workspace_bytes(const ab_gemm_args* args);
 
 /* ---- K1 small-channel direct conv (conv_in / conv_out, Cin or Cout < 64) ------------------------ */
@@ -122,6 +137,18 @@ typedef struct {
   int dtype;
 } ab_attn_args;
 int ab_flash_attn(const ab_attn_args* args, void* stream);
+/* patch-parallel attention: K/V of source s at k_ptrs[s]/v_ptrs[s] ([B, lk_per_src, H, D], strides from args->k_*),
+ * global key order = source 0, 1, ...; head_dim <= 64; bit-identical to ab_flash_attn on the concatenation.
+ * No counterpart in the reference. */
+int ab_flash_attn_multi(const ab_attn_args* args, const void* const* k_ptrs, const void* const* v_ptrs, int nsrc,
+                        int lk_per_src, void* stream);
+/* peer-memory runtime (csrc/peer.cu): cudaMalloc'ed heap + CUDA IPC mapping + device-side barrier */
+int ab_heap_alloc(void** ptr, size_t bytes);
+int ab_heap_free(void* ptr);
+int ab_ipc_get_handle(void* ptr, unsigned char* handle64);
+int ab_ipc_open_handle(const unsigned char* handle64, void** ptr);
+int ab_ipc_close_handle(void* ptr);
+int ab_peer_barrier(void* const* flag_ptrs, int rank, int world, unsigned int epoch, void* stream);
 
 /* ---- K12/K15/G1/G3/S11: elementwise ------------------------------------------------------------- */
 /* counter-based N(0,1): out[i] = normal(philox4x32-10(seed, stream_id, offset + i)); i is the GLOBAL
