@@ -178,6 +178,44 @@ def conv3x3_strided(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torc
     return y.reshape(b, ho, wo, -1)
 
 
+def pack_temporal_conv_weight(w: torch.Tensor) -> torch.Tensor:
+    """Conv3d weight [Cout, Cin, 3, 1, 1] -> [Cout, 3*Cin] with K ordered (kf, cin)."""
+    co, ci = w.shape[0], w.shape[1]
+    return w.reshape(co, ci, 3).permute(0, 2, 1).reshape(co, 3 * ci).contiguous()
+
+
+def conv_temporal(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
+                  residual: Optional[torch.Tensor] = None, act: Optional[str] = None, splitk: int = 0,
+                  block_n: int = 0) -> torch.Tensor:
+    """Temporal Conv3d (3,1,1), pad (1,0,0), on channels-last video x [B, F, HW, C] -> [B, F, HW, Cout].
+    Same implicit-GEMM kernel as conv3x3 with a 3x1 tap pattern over the (F, HW) "image"."""
+    lib = native.load()
+    b, f, hw, c = x.shape
+    assert x.is_contiguous() and w_packed.is_contiguous() and w_packed.shape[1] == 3 * c
+    n = w_packed.shape[0]
+    out = torch.empty((b, f, hw, n), dtype=x.dtype, device=x.device)
+    a = GemmArgs()
+    a.a, a.w, a.out = x.data_ptr(), w_packed.data_ptr(), out.data_ptr()
+    a.bias, a.residual = native.ptr(bias), native.ptr(residual)
+    a.M, a.N, a.K1, a.K2 = b * f * hw, n, c, 0
+    a.conv, a.nimg, a.H, a.W = 2, b, f, hw
+    a.act, a.out_scale = ACT[act], 1.0
+    a.dtype = native.dtype_code(x.dtype)
+    key = f"tconv:{b}x{f}x{hw}:{n}:{c}"
+    if RECORD is not None:
+        RECORD.append(key)
+    cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
+    if cfg is not None:
+        a.block_n, a.splitk = cfg[0], cfg[1]
+    else:
+        a.block_n = block_n
+        a.splitk = splitk if splitk > 0 else auto_splitk(a.M, n, 3 * c // 64)
+    if a.splitk > 1:
+        a.workspace = _workspace(a.splitk * a.M * n * 4, x.device).data_ptr()
+    native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm(temporal conv)")
+    return out
+
+
 class DirectConvWeight:
     """Weight of a small-channel conv in the layout ab_conv_direct wants for its shape class:
     [Cout, kh, kw, Cin] when Cout <= 8 (warp-per-pixel kernel), else [kh, kw, Cin, Cout]."""

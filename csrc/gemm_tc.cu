@@ -227,7 +227,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const CUtensorMap* ma = second ? &tmA2 : &tmA;
                 const int c0 = (second ? cc - p.k1_chunks : cc) * BK;
                 if (p.conv) {
-                    const int dh = tap / 3 - 1, dw = tap % 3 - 1;
+                    // conv == 1: 3x3 taps; conv == 2: 3x1 taps along H only (temporal Conv3d (3,1,1) on [B, F, HW, C])
+                    const int dh = p.conv == 2 ? tap - 1 : tap / 3 - 1;
+                    const int dw = p.conv == 2 ? 0 : tap % 3 - 1;
                     tma_load_4d(sa, ma, &full_bar[stage], c0, w0 + dw, h0 + dh, i0);
                 } else {
                     if (p.nsrc > 1) {
@@ -516,7 +518,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     p.workspace = reinterpret_cast<float*>(a->workspace);
     p.dbg = g_gemm_dbg;
     p.M = a->M; p.N = a->N; p.Nout = a->geglu ? a->N / 2 : a->N;
-    p.taps = a->conv ? 9 : 1;
+    p.taps = a->conv == 2 ? 3 : (a->conv ? 9 : 1);
     p.k1_chunks = (a->K2 > 0 || a->conv) ? a->K1 / BK : (a->K1 + BK - 1) / BK;
     p.k2_chunks = a->K2 > 0 ? (a->conv ? a->K2 / BK : (a->K2 + BK - 1) / BK) : 0;
     p.conv = a->conv; p.nimg = a->nimg; p.H = a->H; p.W = a->W;

@@ -142,6 +142,23 @@ int ab_flash_attn(const ab_attn_args* args, void* stream);
  * No counterpart in the reference. */
 int ab_flash_attn_multi(const ab_attn_args* args, const void* const* k_ptrs, const void* const* v_ptrs, int nsrc,
                         int lk_per_src, void* stream);
+/* ---- K8: temporal self-attention of the video UNets (csrc/temporal_attn.cu) -----------------------------
+ * q/k/v/out are channels-last video tensors [B, F_s, HW, heads*D] (token rows of `row_stride` elements, so q, k, v
+ * may be column slices of one fused QKV projection). Every pixel attends over its F frames. With nsrc > 1 the
+ * frame axis is sharded over nsrc buffers (sequence parallelism; pointers may be peer-mapped): the kernel pulls
+ * each source's frames into its tile and scatters output rows back to the buffer that owns the frame.
+ * ref: SDPA on a permuted [B*HW, F, C] tensor inside diffusers' TransformerTemporalModel.                    */
+typedef struct {
+  const void* q[8]; const void* k[8]; const void* v[8]; void* out[8];
+  int nsrc;                 /* 0 or 1 = single buffer */
+  int batch, heads, frames, hw, head_dim;
+  long long row_stride;     /* elements between consecutive tokens of q/k/v */
+  long long out_row_stride;
+  float scale;              /* 0 = 1/sqrt(head_dim) */
+  int dtype;
+} ab_temporal_attn_args;
+int ab_temporal_attn(const ab_temporal_attn_args* args, void* stream);
+
 /* peer-memory runtime (csrc/peer.cu): cudaMalloc'ed heap + CUDA IPC mapping + device-side barrier */
 int ab_heap_alloc(void** ptr, size_t bytes);
 int ab_heap_free(void* ptr);
