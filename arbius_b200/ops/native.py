@@ -51,6 +51,7 @@ class GroupNormArgs(C.Structure):
         ("act", C.c_int),
         ("dtype", C.c_int),
         ("scale", C.c_void_p), ("shift", C.c_void_p),
+        ("ss_stride", C.c_int),
     ]
 
 

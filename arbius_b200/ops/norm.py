@@ -42,6 +42,9 @@ def groupnorm(x: torch.Tensor, gamma: Optional[torch.Tensor], beta: Optional[tor
     a.eps, a.act = eps, ACT[act]
     a.dtype = native.dtype_code(x.dtype)
     a.scale, a.shift = native.ptr(scale), native.ptr(shift)
+    if scale is not None and scale.dim() == 2:
+        assert shift is None or shift.stride(0) == scale.stride(0)
+        a.ss_stride = scale.stride(0)              # scale/shift may be column slices of one fused projection
     native.check(lib.ab_groupnorm(C.byref(a), native.stream_ptr()), "ab_groupnorm")
     return y
 

@@ -36,6 +36,7 @@ struct GnParams {
     int n, hw, c1, c2, groups, sub;
     float eps;
     int act;
+    int ss;                  // row stride (elements) of scale/shift
 };
 
 // workspace layout: counters (n * 4 B, padded to 256) | stats (n*groups*8 B, padded to 256) | partials
@@ -202,8 +203,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const GnParams p) 
             float ga[8], be[8], sc[8], sh[8];
             if (gamma) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
             if (beta) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(beta + c)), be);
-            if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * C + c)), sc);
-            if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * C + c)), sh);
+            if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * p.ss + c)), sc);
+            if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * p.ss + c)), sh);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const float2 st = __ldg(&p.stats[n * p.groups + (c + i) / cpg]);
@@ -314,7 +315,7 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     p.partials = reinterpret_cast<float4*>(ws + gn_counters_bytes(a->n) + gn_stats_bytes(a->n, a->groups));
     p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
     p.sub = gn_sub_blocks(a->hw);
-    p.eps = a->eps; p.act = a->act;
+    p.eps = a->eps; p.act = a->act; p.ss = a->ss_stride > 0 ? a->ss_stride : C;
     const int ncol = C / 8;
     const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
     const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
@@ -411,7 +412,7 @@ extern "C" int ab_groupnorm_static(const ab_groupnorm_args* a, void* stream_) {
     p.partials = reinterpret_cast<float4*>(ws + kStaticCountersBytes + kStaticStatsBytes);
     p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
     p.sub = gn_sub_blocks(a->hw);
-    p.eps = a->eps; p.act = a->act;
+    p.eps = a->eps; p.act = a->act; p.ss = a->ss_stride > 0 ? a->ss_stride : C;
     const int ncol = C / 8;
     const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
     const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);

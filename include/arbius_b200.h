@@ -101,6 +101,7 @@ typedef struct {
   int dtype;
   /* optional per-(n, channel) scale/shift applied after the affine: y = y*(1+scale)+shift */
   const void* scale; const void* shift;
+  int ss_stride;            /* row stride of scale/shift in elements, 0 = C1+C2 */
 } ab_groupnorm_args;
 int ab_groupnorm(const ab_groupnorm_args* args, void* stream);
 size_t ab_groupnorm_partials_bytes(int n, int groups);
@@ -113,6 +114,21 @@ size_t ab_groupnorm_partials_bytes(int n, int groups);
  * counters are cleared on `stream` before each launch, and calls that overlap on one GPU race, so
  * serialise them. Calls no cudaMalloc/cudaFree. No counterpart in the reference (it has no native code). */
 int ab_groupnorm_static(const ab_groupnorm_args* args, void* stream);
+
+/* ---- K11/K14/K16 helpers (csrc/elementwise2.cu), all NHWC, C % 8 == 0 ----------------------------------- */
+/* 2x2 average pooling (guided-diffusion "resblock down") */
+int ab_avgpool2x(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
+/* MoVQ SpatialNorm tail: out = act(x * ymap[up] + bmap[up]); ymap/bmap [N, lh, lw, C] nearest-upsampled to [h, w] */
+int ab_spatial_modulate(const void* x, const void* ymap, const void* bmap, void* out, int n, int h, int w, int c,
+                        int lh, int lw, int act, int dtype, void* stream);
+/* RVM ConvGRU: out = (1 - z) * hprev + z * tanh(cand) */
+int ab_gru_update(const void* z, const void* cand, const void* hprev, void* out, long long n, int dtype, void* stream);
+/* depthwise KxK conv (K = 3 | 5), stride 1 | 2, dilation, pad = (K/2)*dilation; weights [K*K, C]; fused bias + act */
+int ab_dwconv(const void* x, const void* w, const void* bias, void* y, int n, int h, int wd, int c, int ksize,
+              int stride, int dilation, int act, int dtype, void* stream);
+/* global average pool [N, HW, C] -> [N, C]; per-(n, channel) scaling y = x * s[n, c] (squeeze-excite) */
+int ab_global_avgpool(const void* x, void* y, int n, int hw, int c, int dtype, void* stream);
+int ab_channel_scale(const void* x, const void* s, void* y, int n, int hw, int c, int dtype, void* stream);
 
 /* ---- K5: LayerNorm over the last dim ------------------------------------------------------------ */
 int ab_layernorm(const void* x, const void* gamma, const void* beta, void* y, int rows, int cols, float eps,
