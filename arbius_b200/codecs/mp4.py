@@ -134,3 +134,19 @@ def demux_samples(data: bytes) -> List[bytes]:
         out.append(data[off:off + s])
         off += s
     return out
+
+
+def probe_fps(data: bytes, default: int = 30) -> int:
+    """frames per second from mdhd timescale / stts sample delta (constant-rate files only)"""
+    try:
+        rng = (0, len(data))
+        for name in (b"moov", b"trak", b"mdia"):
+            rng = next((s, e) for t, s, e in parse_boxes(data, *rng) if t == name)
+        mdhd = next((s, e) for t, s, e in parse_boxes(data, *rng) if t == b"mdhd")
+        timescale = struct.unpack(">I", data[mdhd[0] + 12:mdhd[0] + 16])[0]
+        for name in (b"minf", b"stbl", b"stts"):
+            rng = next((s, e) for t, s, e in parse_boxes(data, *rng) if t == name)
+        delta = struct.unpack(">I", data[rng[0] + 12:rng[0] + 16])[0]
+        return max(1, round(timescale / delta))
+    except (StopIteration, struct.error, ZeroDivisionError):
+        return default

@@ -217,6 +217,52 @@ int ab_timestep_embedding(const float* t, void* out, int batch, int dim, int fli
 int ab_matting_composite(const void* fgr, const void* pha, unsigned char* out, long long npix, int mode,
                          int dtype, void* stream);
 
+/* ---------------------------------------------------------------- matting (csrc/matting.cu) ---
+ * Small-channel direct convolution on the CUDA cores for the shapes the tensor-core path cannot tile
+ * (RVM decoder: 171/107/59/35 input channels, 3-channel image sources). NHWC, up to three virtually
+ * concatenated sources, each a (pointer, channels, row stride) triple so channel slices of a wider tensor
+ * are sources without a copy. Optional per-source multiplicative gate (ConvGRU r*h), optional input affine
+ * on source 0 (ImageNet normalisation; applied to in-bounds pixels only, padding stays zero), optional
+ * ConvGRU epilogue out = (1-z)*h + z*act(acc).
+ * w: [ks*ks*(c0+c1+c2), cout_pad] with cout_pad = round_up(cout, 16), model dtype. bias: [cout] model dtype. */
+typedef struct ab_conv_generic_args {
+    const void* src[3];
+    const void* gate[3];
+    int c[3], ld[3], gate_ld[3];
+    int nsrc;
+    const void* w;
+    const void* bias;
+    const float* in_scale;
+    const float* in_shift;
+    void* out;
+    int out_ld;
+    const void* gru_z;
+    const void* gru_h;
+    int gru_z_ld, gru_h_ld;
+    int n, h, w_in, ks, stride, dilation, cout, act, dtype;
+} ab_conv_generic_args;
+int ab_conv_generic(const ab_conv_generic_args* args, void* stream);
+/* bilinear resize with explicit source-step (PyTorch align_corners=False with a given scale_factor):
+ * src index = (dst + 0.5) * step - 0.5, clamped. in_u8 = 1: x is uint8 and the output is x/255. */
+int ab_resize_bilinear_ex(const void* x, int ldx, void* y, int ldy, int n, int h, int w, int c, int oh, int ow,
+                          float step_h, float step_w, int in_u8, int dtype, void* stream);
+/* 2x2 average pool, ceil_mode, count_include_pad=False, any h/w/c */
+int ab_avgpool2x_ceil(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
+/* rows x cols strided copy to one or two destinations (dst2 may be NULL) */
+int ab_copy_cols(const void* src, int ld_src, void* dst1, int ld1, void* dst2, int ld2, long long rows, int cols,
+                 int dtype, void* stream);
+/* deep guided filter, low-res half: base_src [n,h,w,3], proj [n,h,w,4] -> stats [n,h,w,8] (cov_xy, var_x),
+ * mean_x [n,h,w,4], mean_y [n,h,w,4]; 3x3 box filter with zero padding (divide by 9 everywhere) */
+int ab_guided_stats(const void* base_src, const void* proj, void* stats, void* mean_x, void* mean_y, int n, int h,
+                    int w, int dtype, void* stream);
+/* deep guided filter, full-res half + output stage: src u8 [N,H,W,3]; refine=1: A/mean_x/mean_y [n,h,w,4] are
+ * bilinearly upsampled (b = mean_y - A*mean_x at low res), out = A*[src,mean(src)] + b; refine=0: proj [N,H,W,4]
+ * at full res. fgr = clamp(out[:3]+src), pha = clamp(out[3]). Writes fgr [N,H,W,3] / pha [N,H,W,1] (model dtype)
+ * when non-NULL and the composited u8 frame (mode as ab_matting_composite) when out_u8 is non-NULL. */
+int ab_guided_apply(const unsigned char* src, const void* a_or_proj, const void* mean_x, const void* mean_y,
+                    void* fgr, void* pha, unsigned char* out_u8, int n, int H, int W, int h, int w, int refine,
+                    int mode, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
