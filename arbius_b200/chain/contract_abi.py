@@ -133,6 +133,9 @@ GOVERNOR_FUNCTIONS: Dict[str, Tuple[List[str], List[str], bool]] = {
     "descriptionHashes": (["uint256"], ["bytes32"], False), "descriptionCids": (["uint256"], ["bytes"], False),
     "hashProposal": (["address[]", "uint256[]", "bytes[]", "bytes32"], ["uint256"], False),
     "timelock": ([], ["address"], False),
+    "getActions": (["uint256"], ["address[]", "uint256[]", "string[]", "bytes[]"], False),
+    "proposals": (["uint256"], ["uint256", "address", "uint256", "uint256", "uint256", "uint256", "uint256", "uint256",
+                                "bool", "bool"], False),
     "propose": (["address[]", "uint256[]", "bytes[]", "string"], ["uint256"], True),
     "castVote": (["uint256", "uint8"], ["uint256"], True),
     "castVoteWithReason": (["uint256", "uint8", "string"], ["uint256"], True),

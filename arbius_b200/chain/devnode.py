@@ -299,6 +299,14 @@ class DevChain:
             return g.hash_proposal(a[0], a[1], a[2], a[3])
         if name == "timelock":
             return self.timelock.address
+        if name in ("getActions", "proposals"):
+            p = g.proposals.get(a[0])
+            if p is None:
+                raise Revert("Governor: unknown proposal id")
+            if name == "getActions":
+                return p.targets, p.values, [""] * len(p.targets), p.calldatas
+            return (a[0], p.proposer, g.proposal_eta(a[0]), p.vote_start, p.vote_end, p.votes[1], p.votes[0], p.votes[2],
+                    g.state(a[0]) == 2, g.state(a[0]) == 7)
         if name == "propose":
             return g.propose(sender, a[0], a[1], a[2], a[3])
         if name == "castVote":
