@@ -86,7 +86,8 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=8, help="timed tasks per GPU")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "eager", "reference"])
-    ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "tiny", "zeroscopev2xl", "damo", "video-tiny"])
+    ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "tiny", "zeroscopev2xl", "damo", "video-tiny",
+                                                              "kandinsky2", "kandinsky-tiny"])
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--denoise-steps", type=int, default=20)
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
@@ -124,6 +125,18 @@ def main() -> int:
                     num_frames=vcfg.default_frames, num_inference_steps=steps_v, width=vcfg.default_size[0],
                     height=vcfg.default_size[1], guidance_scale=vcfg.default_guidance)
         out_name, model_desc = "out-1.mp4", f"{args.model} UNet3D {vcfg.default_size[0]}x{vcfg.default_size[1]}x{vcfg.default_frames}, {steps_v} steps"
+        shape_desc = {"image": f"{vcfg.default_size[0]}x{vcfg.default_size[1]}x{vcfg.default_frames}f", "denoise_steps": steps_v,
+                      "scheduler": "DDIM" if args.model == "zeroscopev2xl" else "DPMSolverMultistep"}
+        arch = "text-to-video UNet3D"
+    elif args.model.startswith("kandinsky"):
+        from arbius_b200.models.kandinsky.pipeline import Kandinsky2Config, Kandinsky2Pipeline
+        kcfg = Kandinsky2Config() if args.model == "kandinsky2" else Kandinsky2Config.tiny()
+        pipe = Kandinsky2Pipeline(kcfg, backend=args.impl, device=f"cuda:{local}", dtype=dt)
+        ksz = 768 if args.model == "kandinsky2" else 32
+        base = dict(prompt="arbius test cat", width=ksz, height=ksz)
+        out_name, model_desc = "out-1.png", f"{args.model} (XLM-R + diffusion prior + UNet 1.2B + MoVQ) {ksz}x{ksz}, {kcfg.steps} steps"
+        shape_desc = {"image": f"{ksz}x{ksz}", "denoise_steps": kcfg.steps, "scheduler": kcfg.sampler}
+        arch = "Kandinsky 2.1"
     else:
         cfg = SD15Config() if args.model == "anythingv3" else SD15Config.tiny()
         pipe = SD15Pipeline(cfg, backend=args.impl, device=f"cuda:{local}", dtype=dt, seed=0)
@@ -132,6 +145,8 @@ def main() -> int:
                     scheduler="DPMSolverMultistep")
         out_name = "out-1.png"
         model_desc = "AnythingV3 (SD-1.5 UNet 860M + CLIP ViT-L/14 + AutoencoderKL)" if args.model == "anythingv3" else "tiny"
+        shape_desc = {"image": f"{args.size}x{args.size}", "denoise_steps": args.denoise_steps, "scheduler": "DPMSolverMultistep"}
+        arch = "SD-1.5"
 
     def barrier():
         if world > 1:
@@ -192,10 +207,9 @@ def main() -> int:
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(dev_ms / K, 3),
         "p50_latency_ms": round(lat_ms[len(lat_ms) // 2], 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": args.dtype, "data": "synthetic prompts, random-init weights of the SD-1.5 architecture",
+        "dtype": args.dtype, "data": f"synthetic prompts, random-init weights of the {arch} architecture",
         "config": {"model": model_desc,
-                   "global_batch": world, "seq_len": 77, "image": f"{args.size}x{args.size}",
-                   "denoise_steps": args.denoise_steps, "cfg_batch": 2, "scheduler": "DPMSolverMultistep",
+                   "global_batch": world, "seq_len": 77, **shape_desc, "cfg_batch": 2,
                    "parallelism": f"task-dp{world}",
                    "l2": f"inputs larger than L2: every task streams {weights_gb:.2f} GB of weights through a 126 MB L2"},
         "clocks": clocks,

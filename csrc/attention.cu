@@ -88,6 +88,8 @@ flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -292,8 +294,7 @@ static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUten
         configured = true;
     }
     dim3 grid((p.lq + ATT_BM - 1) / ATT_BM, p.heads, p.batch);
-    flash_attn_kernel<NCH, T><<<grid, ATT_THREADS, smem, stream>>>(tq, tk, tv, p);
-    AB_CHECK_CUDA(cudaGetLastError());
+    AB_CHECK_CUDA(launch_pdl(flash_attn_kernel<NCH, T>, grid, dim3(ATT_THREADS), smem, stream, tq, tk, tv, p));
     ab_count_launch(1);
     return 0;
 }

@@ -73,6 +73,8 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -288,8 +290,7 @@ static int launch_attn2_multi(const CUtensorMap& tq, const KvMaps<NSRC>& kv, con
         configured = true;
     }
     dim3 grid((p.lq + 255) / 256, p.heads, p.batch);
-    flash_attn2_kernel<T, NSRC><<<grid, A2_THREADS, smem, stream>>>(tq, kv, p);
-    AB_CHECK_CUDA(cudaGetLastError());
+    AB_CHECK_CUDA(launch_pdl(flash_attn2_kernel<T, NSRC>, grid, dim3(A2_THREADS), smem, stream, tq, kv, p));
     ab_count_launch(1);
     return 0;
 }

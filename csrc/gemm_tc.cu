@@ -6,8 +6,9 @@
 //                         the NHWC image fetched by a 4-D TMA box whose start coordinate is shifted
 //                         by the tap offset — TMA's out-of-bounds zero fill IS the padding.
 //   * virtual concat:     a second A source appended along K (skip connections never get copied)
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
-// warps 2..5 = epilogue (tcgen05.ld -> bias/time-emb/activation/GEGLU/residual -> global).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
+// warps 2..9 = epilogue (tcgen05.ld -> bias/time-emb/activation/GEGLU/residual -> global), two warps per
+// TMEM lane quarter on alternate 32-column chunks with the next chunk's tcgen05.ld in flight.
 // Accumulators live in TMEM (128 lanes x BN fp32 columns). Two CTAs fit per SM (<=113 KB smem,
 // <=256 TMEM columns each) so one CTA's epilogue overlaps the other's main loop.
 // Split-K is a fixed, caller-chosen factor with an in-order second pass: results never depend on
@@ -27,7 +28,7 @@ namespace ab {
 constexpr int BM = 128;      // rows per tile == TMEM lanes
 constexpr int BK = 64;       // 64 x 16-bit = one 128-byte swizzle row
 constexpr int UK = 16;       // K per tcgen05.mma for 16-bit inputs
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quarter)
 
 struct GemmParams {
     void* out;
@@ -55,7 +56,12 @@ struct GemmParams {
     // workspace of the rank that owns m; owners then sum the 8 canonical K shards in order.
     int rows_per_owner, z_base;
     float* ws_peer[8];
+    // Output through TMA: the epilogue stages each 128-row x 32-column box in shared memory (reusing the drained
+    // pipeline stages) and one thread issues a bulk tensor store — full-line writes instead of 16-byte pieces
+    // scattered over 32 rows per warp instruction. Off for GEGLU, split-K partials and reduce-scatter.
+    int tma_store;
     alignas(64) CUtensorMap amaps[8];
+    alignas(64) CUtensorMap omap;
 };
 
 template <typename T>
@@ -80,7 +86,8 @@ __device__ __forceinline__ float epi_act(float x, int act) {
 // Epilogue for one row x 32 accumulator columns starting at global column n_base.
 template <typename T, int EPI>
 __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long out_row, int grp, int n_base,
-                                                 float (&v)[32], const float* sb, bool rowbias_global) {
+                                                 float (&v)[32], const float* sb, bool rowbias_global,
+                                                 uint8_t* stage_row = nullptr, int stage_swz = 0) {
     const T* bias = reinterpret_cast<const T*>(p.bias);
     const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
     const T* residual = reinterpret_cast<const T*>(p.residual);
@@ -143,14 +150,19 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
 #pragma unroll
                     for (int i = 0; i < 8; ++i) o[i] += r[i];
                 }
-                *reinterpret_cast<uint4*>(out + out_row * p.ldo + n) = pack8<T>(o);
+                if (stage_row) {
+                    // 64-byte rows in the SWIZZLE_64B pattern of the output tensor map: 16-byte slot g ^ ((row >> 1) & 3)
+                    *reinterpret_cast<uint4*>(stage_row + ((g ^ stage_swz) << 4)) = pack8<T>(o);
+                } else {
+                    *reinterpret_cast<uint4*>(out + out_row * p.ldo + n) = pack8<T>(o);
+                }
             }
         }
     }
 }
 
 template <int BN, int STAGES, typename T, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS)
+__global__ void __launch_bounds__(GEMM_THREADS, (BN > 160 ? 1 : 2))
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ GemmParams p) {
     constexpr int A_BYTES = BM * BK * 2;
@@ -209,6 +221,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // everything above overlapped the previous kernel's tail; operands/outputs are only touched past this point
+    pdl_wait();
+    pdl_launch_dependents();
     if (dbg && threadIdx.x == 32) dbg[0] = clock64() - t_start;   // setup done
 
     if (warp == 0) {
@@ -270,6 +285,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else {
         // ================= epilogue warps =================
         const int q = warp & 3;                   // TMEM lane quarter this warp may read
+        const int hf = (warp - 2) >> 2;           // which half of the 32-column chunks this warp handles
         const int r = q * 32 + lane;              // row inside the tile
         long long out_row;
         int grp;
@@ -300,7 +316,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (use_sb) {
             const T* bias = reinterpret_cast<const T*>(p.bias);
             const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
-            for (int n = threadIdx.x - 64; n < BN; n += 128) {
+            for (int n = threadIdx.x - 64; n < BN; n += GEMM_THREADS - 64) {
                 float b = 0.f;
                 if (n0 + n < p.N) {
                     if (bias) b = DT<T>::to_f(bias[n0 + n]);
@@ -308,23 +324,52 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 sbias[n] = b;
             }
-            asm volatile("bar.sync 1, 128;\n" ::: "memory");
+            asm volatile("bar.sync 1, 256;\n" ::: "memory");
         }
         const bool rowbias_global = !single_group;
         mbar_wait(acc_bar, 0);
         tc_fence_after();
         if (dbg && threadIdx.x == 64) dbg[3] = clock64() - t_start;   // accumulator ready
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-#pragma unroll 2
-        for (int c = 0; c < BN / 32; ++c) {
-            uint32_t raw[32];
-            tmem_ld32(taddr + c * 32, raw);
+        // Two warps share each TMEM lane quarter and take alternate 32-column chunks; the tcgen05.ld of a warp's
+        // next chunk is in flight while it converts and stores the current one.
+        constexpr int NCHUNK = BN / 32;
+        constexpr int MY_MAX = (NCHUNK + 1) / 2;
+        // (the prefetch needs a second 32-register buffer: only where one CTA per SM leaves the registers free)
+        constexpr bool PF = BN > 160;
+        uint32_t raw[PF ? 2 : 1][32];
+        if (PF && hf < NCHUNK) tmem_ld32(taddr + hf * 32, raw[0]);
+#pragma unroll
+        for (int j = 0; j < MY_MAX; ++j) {
+            const int c = 2 * j + hf;
+            if (c >= NCHUNK) break;
+            if (!PF) tmem_ld32(taddr + c * 32, raw[0]);
             tmem_wait_ld();
+            if (PF && j + 1 < MY_MAX && c + 2 < NCHUNK) tmem_ld32(taddr + (c + 2) * 32, raw[PF ? ((j + 1) & 1) : 0]);
             const int n_base = n0 + c * 32;
+            if (p.tma_store) {
+                if (n_base >= p.N) continue;                           // warp-uniform: the whole box is out of range
+                uint8_t* box = smem + c * (BM * 64);
+                if (row_ok) {
+                    float v[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
+                    epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias + c * 32, rowbias_global, box + r * 64,
+                                             (r >> 1) & 3);
+                }
+                fence_proxy_async();
+                asm volatile("bar.sync %0, 128;\n" ::"r"(2 + hf) : "memory");   // the four warps of this chunk parity
+                if (q == 0 && lane == 0) {
+                    if (p.conv) tma_store_4d(&p.omap, box, n_base, w0, h0, i0);
+                    else tma_store_2d(&p.omap, box, n_base, m0);
+                    tma_store_commit();
+                }
+                continue;
+            }
             if (row_ok && n_base < p.N) {
                 float v[32];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
                 if (p.splitk > 1) {
                     const int owner = static_cast<int>(out_row / p.rows_per_owner);
                     float* ws = p.ws_peer[owner] + (static_cast<long long>(p.z_base + blockIdx.z) * p.rows_per_owner +
@@ -338,6 +383,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             }
         }
+        if (p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
     }
 
     if (dbg && threadIdx.x == 64) dbg[4] = clock64() - t_start;       // epilogue done
@@ -351,6 +397,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // Second pass of split-K: sum the fp32 partial tiles in split order, then the normal epilogue.
 template <typename T, int EPI>
 __global__ void splitk_reduce_kernel(const GemmParams p) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int chunks_n = (p.N + 31) / 32;
     const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<long long>(p.M) * chunks_n) return;
@@ -465,8 +513,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CU
         AB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, T, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
-    gemm_tc_kernel<BN, STAGES, T, EPI><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmA2, tmB, p);
-    AB_CHECK_CUDA(cudaGetLastError());
+    AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
     ab_count_launch(1);
     return 0;
 }
@@ -620,6 +667,24 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         if (ab_make_tensor_map(&tmB, a->dtype, 2, a->w, dims, str, box, 128)) return -1;
     }
 
+    static const bool tma_store_on = [] { const char* e = getenv("AB_TMA_STORE"); return !(e && e[0] == '0'); }();
+    p.tma_store = 0;
+    if (tma_store_on && !a->geglu && splitk <= 1 && !rs && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0) {
+        const uint64_t ld = (uint64_t)p.ldo * esz;
+        if (a->conv) {
+            uint64_t dims[4] = {(uint64_t)a->N, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
+            uint64_t str[3] = {ld, (uint64_t)a->W * ld, (uint64_t)a->H * a->W * ld};
+            uint32_t box[4] = {32, (uint32_t)ct.bw, (uint32_t)ct.bh, (uint32_t)ct.bi};
+            if (ab_make_tensor_map(&p.omap, a->dtype, 4, a->out, dims, str, box, 64)) return -1;
+        } else {
+            uint64_t dims[2] = {(uint64_t)a->N, (uint64_t)a->M};
+            uint64_t str[1] = {ld};
+            uint32_t box[2] = {32, BM};
+            if (ab_make_tensor_map(&p.omap, a->dtype, 2, a->out, dims, str, box, 64)) return -1;
+        }
+        p.tma_store = 1;
+    }
+
     dim3 grid(tiles_m, (a->N + bn - 1) / bn, grid_z);
     int epi = a->geglu ? EPI_GEGLU
             : a->act == ACT_NONE ? EPI_NONE
@@ -650,12 +715,12 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         const int blocks = static_cast<int>((work + threads - 1) / threads);
 #define AB_RED_EPI(T)                                                                                      \
     switch (epi) {                                                                                         \
-        case EPI_NONE: splitk_reduce_kernel<T, EPI_NONE><<<blocks, threads, 0, stream>>>(p); break;        \
-        case EPI_SILU: splitk_reduce_kernel<T, EPI_SILU><<<blocks, threads, 0, stream>>>(p); break;        \
-        case EPI_GELU: splitk_reduce_kernel<T, EPI_GELU><<<blocks, threads, 0, stream>>>(p); break;        \
-        case EPI_QGELU: splitk_reduce_kernel<T, EPI_QGELU><<<blocks, threads, 0, stream>>>(p); break;      \
-        case EPI_GEGLU: splitk_reduce_kernel<T, EPI_GEGLU><<<blocks, threads, 0, stream>>>(p); break;      \
-        default: splitk_reduce_kernel<T, EPI_ANY><<<blocks, threads, 0, stream>>>(p); break;               \
+        case EPI_NONE: launch_pdl(splitk_reduce_kernel<T, EPI_NONE>, dim3(blocks), dim3(threads), 0, stream, p); break;        \
+        case EPI_SILU: launch_pdl(splitk_reduce_kernel<T, EPI_SILU>, dim3(blocks), dim3(threads), 0, stream, p); break;        \
+        case EPI_GELU: launch_pdl(splitk_reduce_kernel<T, EPI_GELU>, dim3(blocks), dim3(threads), 0, stream, p); break;        \
+        case EPI_QGELU: launch_pdl(splitk_reduce_kernel<T, EPI_QGELU>, dim3(blocks), dim3(threads), 0, stream, p); break;      \
+        case EPI_GEGLU: launch_pdl(splitk_reduce_kernel<T, EPI_GEGLU>, dim3(blocks), dim3(threads), 0, stream, p); break;      \
+        default: launch_pdl(splitk_reduce_kernel<T, EPI_ANY>, dim3(blocks), dim3(threads), 0, stream, p); break;               \
     }
         if (a->dtype == AB_BF16) { AB_RED_EPI(__nv_bfloat16) } else { AB_RED_EPI(__half) }
 #undef AB_RED_EPI

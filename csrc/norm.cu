@@ -66,6 +66,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
     const int ncol = C / 8;
     const int cpg = C / p.groups;
     const int n = blockIdx.z, shard = blockIdx.y, sub = blockIdx.x;
+    pdl_wait();
+    pdl_launch_dependents();
     const int s_begin = static_cast<int>((static_cast<long long>(shard) * p.hw) / GN_SHARDS);
     const int s_end = static_cast<int>((static_cast<long long>(shard + 1) * p.hw) / GN_SHARDS);
     const int len = s_end - s_begin;
@@ -183,6 +185,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const GnParams p) 
     const int RL = GN_THREADS / cols;
     const int passes = (ncol + cols - 1) / cols;
     const int rl = threadIdx.x / cols;
+    pdl_wait();
+    pdl_launch_dependents();
     if (rl >= RL) return;
     const int r_begin = blockIdx.x * (RL * GN_APPLY_ROWS);
     const int r_end = min(p.hw, r_begin + RL * GN_APPLY_ROWS);
@@ -240,6 +244,8 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x,
                                                         const T* __restrict__ beta, T* __restrict__ y, int rows,
                                                         int cols, float eps) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    pdl_wait();
+    pdl_launch_dependents();
     if (row >= rows) return;
     const int lane = threadIdx.x & 31;
     const int nvec = cols / 8;
@@ -325,11 +331,11 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     const int apply_rows = (GN_THREADS / apply_cols) * GN_APPLY_ROWS;
     dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
-        gn_stats_kernel<__nv_bfloat16><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__nv_bfloat16><<<blocks, GN_THREADS, 0, stream>>>(p);
+        AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__nv_bfloat16>, grid, dim3(GN_THREADS), smem, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_THREADS), 0, stream, p));
     } else {
-        gn_stats_kernel<__half><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__half><<<blocks, GN_THREADS, 0, stream>>>(p);
+        AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__half>, grid, dim3(GN_THREADS), smem, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_THREADS), 0, stream, p));
     }
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(2);
@@ -424,11 +430,11 @@ extern "C" int ab_groupnorm_static(const ab_groupnorm_args* a, void* stream_) {
     const int apply_rows = (GN_THREADS / apply_cols) * GN_APPLY_ROWS;
     dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
-        gn_stats_kernel<__nv_bfloat16><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__nv_bfloat16><<<blocks, GN_THREADS, 0, stream>>>(p);
+        AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__nv_bfloat16>, grid, dim3(GN_THREADS), smem, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_THREADS), 0, stream, p));
     } else {
-        gn_stats_kernel<__half><<<grid, GN_THREADS, smem, stream>>>(p);
-        gn_apply_kernel<__half><<<blocks, GN_THREADS, 0, stream>>>(p);
+        AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__half>, grid, dim3(GN_THREADS), smem, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_THREADS), 0, stream, p));
     }
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(2);
@@ -445,10 +451,9 @@ extern "C" int ab_layernorm(const void* x, const void* gamma, const void* beta, 
     const int blocks = (rows + warps - 1) / warps;
     const int nvec = cols / 8;
 #define AB_LN(T, MAXV)                                                                                              \
-    layernorm_kernel<T, MAXV><<<blocks, warps * 32, 0, stream>>>(reinterpret_cast<const T*>(x),                    \
-                                                                  reinterpret_cast<const T*>(gamma),                \
-                                                                  reinterpret_cast<const T*>(beta),                 \
-                                                                  reinterpret_cast<T*>(y), rows, cols, eps)
+    launch_pdl(layernorm_kernel<T, MAXV>, dim3(blocks), dim3(warps * 32), 0, stream, reinterpret_cast<const T*>(x), \
+               reinterpret_cast<const T*>(gamma), reinterpret_cast<const T*>(beta), reinterpret_cast<T*>(y), rows,  \
+               cols, eps)
     if (dtype == AB_BF16) {
         if (nvec <= 64) AB_LN(__nv_bfloat16, 2); else if (nvec <= 160) AB_LN(__nv_bfloat16, 5); else if (nvec <= 256) AB_LN(__nv_bfloat16, 8); else AB_LN(__nv_bfloat16, 16);
     } else {

@@ -76,6 +76,8 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -222,9 +224,8 @@ extern "C" int ab_temporal_attn(const ab_temporal_attn_args* a, void* stream_) {
         AB_CHECK_CUDA(cudaFuncSetAttribute(temporal_attn_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
-    if (a->dtype == AB_BF16) temporal_attn_kernel<__nv_bfloat16><<<grid, TA_THREADS, smem, stream>>>(maps, p);
-    else temporal_attn_kernel<__half><<<grid, TA_THREADS, smem, stream>>>(maps, p);
-    AB_CHECK_CUDA(cudaGetLastError());
+    if (a->dtype == AB_BF16) AB_CHECK_CUDA(launch_pdl(temporal_attn_kernel<__nv_bfloat16>, grid, dim3(TA_THREADS), smem, stream, maps, p));
+    else AB_CHECK_CUDA(launch_pdl(temporal_attn_kernel<__half>, grid, dim3(TA_THREADS), smem, stream, maps, p));
     ab_count_launch(1);
     return 0;
 }

@@ -25,6 +25,9 @@ const char* ab_last_error(void);
 int ab_version(void);
 /* number of kernel launches issued through this library since load (bench.py gpu_launches) */
 unsigned long long ab_launch_count(void);
+/* programmatic dependent launch between consecutive kernels of this library (default off; AB_PDL=1 enables) */
+int ab_pdl_enabled(void);
+void ab_set_pdl(int on);
 
 enum { AB_F16 = 0, AB_BF16 = 1 };
 enum {

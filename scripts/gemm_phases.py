@@ -4,7 +4,8 @@ from arbius_b200 import ops
 lib = ops.native.load()
 lib.ab_gemm_set_debug.argtypes = [C.c_void_p]; lib.ab_gemm_set_debug.restype = None
 dt = torch.float16
-for (m, n, k, bn) in [(154, 768, 768, 32), (8192, 320, 320, 96), (512, 1280, 1280, 32), (4, 1280, 320, 32), (8192,8192,8192,256)]:
+for (m, n, k, bn) in [(8192, 320, 320, 160), (2048, 640, 640, 96), (512, 1280, 1280, 64), (8192, 1280, 320, 160),
+                      (8192, 320, 2880, 160), (8192, 8192, 8192, 256)]:
     x = torch.randn(m, k, device="cuda", dtype=dt); w = torch.randn(n, k, device="cuda", dtype=dt); b = torch.randn(n, device="cuda", dtype=dt)
     for _ in range(2): ops.gemm(x, w, b, block_n=bn, splitk=1)
     torch.cuda.synchronize()

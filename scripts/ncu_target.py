@@ -7,7 +7,7 @@ what = sys.argv[1] if len(sys.argv) > 1 else "gemm"
 dt = torch.float16
 torch.manual_seed(0)
 if what == "gemm":
-    for (m, n, k, bn) in [(154, 768, 768, 32), (8192, 320, 320, 96), (512, 1280, 1280, 32)]:
+    for (m, n, k, bn) in [(8192, 320, 320, 160), (8192, 1280, 320, 160), (2048, 640, 640, 96)]:
         x = torch.randn(m, k, device="cuda", dtype=dt); w = torch.randn(n, k, device="cuda", dtype=dt); b = torch.randn(n, device="cuda", dtype=dt)
         for _ in range(3):
             ops.gemm(x, w, b, block_n=bn, splitk=1)
