@@ -288,11 +288,7 @@ static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUten
     constexpr int STAGES = NCH >= 3 ? 1 : 2;
     constexpr int PBUF = NCH >= 3 ? 1 : 2;
     constexpr int smem = NCH * CHUNK_BYTES * (1 + 2 * STAGES) + PBUF * 2 * CHUNK_BYTES + 16 * 8 + 16 + 1024;
-    static bool configured = false;
-    if (!configured) {
-        AB_CHECK_CUDA(cudaFuncSetAttribute(flash_attn_kernel<NCH, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
-    }
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(flash_attn_kernel<NCH, T>), smem)) return -1;
     dim3 grid((p.lq + ATT_BM - 1) / ATT_BM, p.heads, p.batch);
     AB_CHECK_CUDA(launch_pdl(flash_attn_kernel<NCH, T>, grid, dim3(ATT_THREADS), smem, stream, tq, tk, tv, p));
     ab_count_launch(1);

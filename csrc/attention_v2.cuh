@@ -284,11 +284,7 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 template <typename T, int NSRC>
 static int launch_attn2_multi(const CUtensorMap& tq, const KvMaps<NSRC>& kv, const AttnParams& p, cudaStream_t stream) {
     constexpr int smem = (2 + 2 * A2_STAGES + 4) * CHUNK_BYTES + 16 * 8 + 16 + 1024;
-    static bool configured = false;
-    if (!configured) {
-        AB_CHECK_CUDA(cudaFuncSetAttribute(flash_attn2_kernel<T, NSRC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
-    }
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(flash_attn2_kernel<T, NSRC>), smem)) return -1;
     dim3 grid((p.lq + 255) / 256, p.heads, p.batch);
     AB_CHECK_CUDA(launch_pdl(flash_attn2_kernel<T, NSRC>, grid, dim3(A2_THREADS), smem, stream, tq, kv, p));
     ab_count_launch(1);

@@ -312,6 +312,8 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 }  // namespace ab
 
 extern "C" int ab_pdl_enabled(void);
+extern "C" int ab_ensure_max_smem(const void* func, int bytes);   // per (kernel, device); returns 0 or -1 (error set)
+extern "C" int ab_sm_count(void);
 namespace ab {
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,

@@ -508,11 +508,7 @@ template <int BN, int STAGES, typename T, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
                        dim3 grid, cudaStream_t stream) {
     constexpr int smem = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 32 + BN * 4 + 1024;
-    static bool configured = false;
-    if (!configured) {
-        AB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, T, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
-    }
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, STAGES, T, EPI>), smem)) return -1;
     AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
     ab_count_launch(1);
     return 0;

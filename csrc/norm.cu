@@ -17,7 +17,7 @@ namespace ab {
 
 constexpr int GN_SHARDS = 8;
 constexpr int GN_MAX_SUB = 32;
-constexpr int GN_THREADS = 256;
+constexpr int GN_THREADS = 512;
 constexpr int GN_MAX_GROUPS = 64;
 
 __host__ __device__ inline int gn_sub_blocks(int hw) {
@@ -40,7 +40,8 @@ struct GnParams {
 };
 
 // workspace layout: counters (n * 4 B, padded to 256) | stats (n*groups*8 B, padded to 256) | partials
-__host__ inline size_t gn_counters_bytes(int n) { return ((size_t)n * 4 + 255) / 256 * 256; }
+// (the two words after the n per-image counters are the fused kernel's grid barrier: arrivals, generation)
+__host__ inline size_t gn_counters_bytes(int n) { return ((size_t)(n + 2) * 4 + 255) / 256 * 256; }
 __host__ inline size_t gn_stats_bytes(int n, int groups) { return ((size_t)n * groups * 8 + 255) / 256 * 256; }
 
 // Parallel-variance merge (Chan et al.): exact-order, fp32, no cancellation between blocks.
@@ -238,6 +239,226 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const GnParams p) 
     }
 }
 
+// ---- fused GroupNorm: statistics + grid barrier + apply in ONE cooperative launch ----------------------
+// Same canonical decomposition and the same arithmetic order as gn_stats_kernel + gn_apply_kernel (bit-identical
+// output), but the rows a CTA reduced stay in its shared memory, so the tensor is read from HBM once, and the second
+// launch (and its drain/ramp) is gone. Items (n, shard, sub) are dealt round-robin to at most one CTA per SM; all CTAs
+// are co-resident (cooperative launch), so the barrier between the phases cannot deadlock.
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+// bar[0] = arrivals, bar[1] = generation; self-resetting, so the same two words serve every call on a stream
+__device__ __forceinline__ void gn_grid_barrier(unsigned int* bar, unsigned int nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int gen = ld_acquire_u32(&bar[1]);
+        __threadfence();
+        const unsigned int ticket = atomicAdd(&bar[0], 1u);
+        if (ticket == nblocks - 1) {
+            bar[0] = 0;
+            __threadfence();
+            st_release_u32(&bar[1], gen + 1);
+        } else {
+            while (ld_acquire_u32(&bar[1]) == gen) __nanosleep(32);
+        }
+    }
+    __syncthreads();
+}
+
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS) gn_fused_kernel(const GnParams p, unsigned int* bar, int cache_rows) {
+    extern __shared__ __align__(16) unsigned char gn_smem[];
+    __shared__ GnMoments shard_mom[GN_SHARDS][GN_MAX_GROUPS + 1];
+    __shared__ float2 s_stats[GN_MAX_GROUPS];
+    const int C = p.c1 + p.c2;
+    const int ncol = C / 8;
+    const int cpg = C / p.groups;
+    const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
+    const int passes = (ncol + GN_THREADS - 1) / GN_THREADS;
+    float* s_sum = reinterpret_cast<float*>(gn_smem);
+    float* s_sq = s_sum + RL * C;
+    uint4* cache = reinterpret_cast<uint4*>(gn_smem + static_cast<size_t>(2) * RL * C * sizeof(float));   // [rows][ncol]
+    const int items_per_img = GN_SHARDS * p.sub;
+    const int total_items = p.n * items_per_img;
+    const bool use_cache = cache_rows > 0;
+
+    auto item_rows = [&](int item, int& n, int& r0, int& r1) {
+        n = item / items_per_img;
+        const int rem = item - n * items_per_img;
+        const int shard = rem / p.sub, sub = rem - shard * p.sub;
+        const int s_begin = static_cast<int>((static_cast<long long>(shard) * p.hw) / GN_SHARDS);
+        const int s_end = static_cast<int>((static_cast<long long>(shard + 1) * p.hw) / GN_SHARDS);
+        const int len = s_end - s_begin;
+        r0 = s_begin + static_cast<int>((static_cast<long long>(sub) * len) / p.sub);
+        r1 = s_begin + static_cast<int>((static_cast<long long>(sub + 1) * len) / p.sub);
+    };
+
+    // ---------------- phase 1: per-item moments (+ keep the rows) ----------------
+    int cached = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        int n, r0, r1;
+        item_rows(item, n, r0, r1);
+        const T* x1 = reinterpret_cast<const T*>(p.x) + static_cast<long long>(n) * p.hw * p.c1;
+        const T* x2 = p.x2 ? reinterpret_cast<const T*>(p.x2) + static_cast<long long>(n) * p.hw * p.c2 : nullptr;
+        for (int pass = 0; pass < passes; ++pass) {
+            int vc, rl;
+            bool active;
+            if (passes == 1) { vc = threadIdx.x % ncol; rl = threadIdx.x / ncol; active = rl < RL; }
+            else { vc = pass * GN_THREADS + threadIdx.x; rl = 0; active = vc < ncol; }
+            if (active) {
+                const int c = vc * 8;
+                const T* src; int ld, cc;
+                if (c < p.c1) { src = x1; ld = p.c1; cc = c; } else { src = x2; ld = p.c2; cc = c - p.c1; }
+                float s[8], q[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
+                const T* ptr = src + static_cast<long long>(r0 + rl) * ld + cc;
+                const long long step = static_cast<long long>(RL) * ld;
+                uint4* cp = cache + static_cast<long long>(cached + rl) * ncol + vc;
+                const long long cstep = static_cast<long long>(RL) * ncol;
+                int r = r0 + rl;
+                for (; r + 3 * RL < r1; r += 4 * RL) {
+                    uint4 v0 = *reinterpret_cast<const uint4*>(ptr);
+                    uint4 v1 = *reinterpret_cast<const uint4*>(ptr + step);
+                    uint4 v2 = *reinterpret_cast<const uint4*>(ptr + 2 * step);
+                    uint4 v3 = *reinterpret_cast<const uint4*>(ptr + 3 * step);
+                    ptr += 4 * step;
+                    if (use_cache) { cp[0] = v0; cp[cstep] = v1; cp[2 * cstep] = v2; cp[3 * cstep] = v3; cp += 4 * cstep; }
+                    float f[8];
+                    unpack8<T>(v0, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                    unpack8<T>(v1, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                    unpack8<T>(v2, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                    unpack8<T>(v3, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                }
+                for (; r < r1; r += RL) {
+                    const uint4 v = *reinterpret_cast<const uint4*>(ptr);
+                    ptr += step;
+                    if (use_cache) { cp[0] = v; cp += cstep; }
+                    float f[8];
+                    unpack8<T>(v, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s_sum[rl * C + c + i] = s[i]; s_sq[rl * C + c + i] = q[i]; }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < p.groups) {
+            const int g = threadIdx.x;
+            float ds = 0.f, dq = 0.f;
+            for (int rl = 0; rl < RL; ++rl)
+                for (int c = g * cpg; c < (g + 1) * cpg; ++c) { ds += s_sum[rl * C + c]; dq += s_sq[rl * C + c]; }
+            const float cnt = static_cast<float>(r1 - r0) * cpg;
+            const float mean = cnt > 0.f ? ds / cnt : 0.f;
+            const float m2 = fmaxf(dq - ds * mean, 0.f);
+            p.partials[static_cast<long long>(item) * p.groups + g] = make_float4(cnt, mean, m2, 0.f);
+            __threadfence();
+        }
+        __syncthreads();
+        cached += r1 - r0;
+    }
+
+    gn_grid_barrier(bar, gridDim.x);
+
+    // ---------------- phase 2 + 3: merge the image's partials in canonical order, then normalise ----------------
+    const T* gamma = reinterpret_cast<const T*>(p.gamma);
+    const T* beta = reinterpret_cast<const T*>(p.beta);
+    const T* scale = reinterpret_cast<const T*>(p.scale);
+    const T* shift = reinterpret_cast<const T*>(p.shift);
+    int stats_n = -1;
+    cached = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        int n, r0, r1;
+        item_rows(item, n, r0, r1);
+        if (n != stats_n) {
+            __syncthreads();
+            const float4* part = p.partials + static_cast<long long>(n) * items_per_img * p.groups;
+            for (int idx = threadIdx.x; idx < GN_SHARDS * p.groups; idx += GN_THREADS) {
+                const int sh = idx / p.groups, g = idx % p.groups;
+                GnMoments acc{0.f, 0.f, 0.f};
+                for (int sb = 0; sb < p.sub; ++sb) {
+                    const float4 q4 = __ldcg(&part[(sh * p.sub + sb) * p.groups + g]);
+                    acc = gn_merge(acc, GnMoments{q4.x, q4.y, q4.z});
+                }
+                shard_mom[sh][g] = acc;
+            }
+            __syncthreads();
+            if (threadIdx.x < p.groups) {
+                const int g = threadIdx.x;
+                GnMoments acc = shard_mom[0][g];
+#pragma unroll
+                for (int sh = 1; sh < GN_SHARDS; ++sh) acc = gn_merge(acc, shard_mom[sh][g]);
+                const float var = acc.m2 / acc.cnt;
+                s_stats[g] = make_float2(acc.mean, rsqrtf(var + p.eps));
+            }
+            __syncthreads();
+            stats_n = n;
+        }
+        T* y = reinterpret_cast<T*>(p.y) + static_cast<long long>(n) * p.hw * C;
+        for (int pass = 0; pass < passes; ++pass) {
+            int vc, rl;
+            bool active;
+            if (passes == 1) { vc = threadIdx.x % ncol; rl = threadIdx.x / ncol; active = rl < RL; }
+            else { vc = pass * GN_THREADS + threadIdx.x; rl = 0; active = vc < ncol; }
+            if (!active) continue;
+            const int c = vc * 8;
+            const T* src; int ld, cc;
+            if (c < p.c1) { src = reinterpret_cast<const T*>(p.x) + static_cast<long long>(n) * p.hw * p.c1; ld = p.c1; cc = c; }
+            else { src = reinterpret_cast<const T*>(p.x2) + static_cast<long long>(n) * p.hw * p.c2; ld = p.c2; cc = c - p.c1; }
+            float a[8], b[8];
+            {
+                float ga[8], be[8], sc[8], sh[8];
+                if (gamma) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
+                if (beta) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(beta + c)), be);
+                if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * p.ss + c)), sc);
+                if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * p.ss + c)), sh);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float2 st = s_stats[(c + i) / cpg];
+                    float ai = st.y, bi = -st.x * st.y;
+                    if (gamma) { ai *= ga[i]; bi *= ga[i]; }
+                    if (beta) bi += be[i];
+                    if (scale) { ai *= (1.0f + sc[i]); bi *= (1.0f + sc[i]); }
+                    if (shift) bi += sh[i];
+                    a[i] = ai; b[i] = bi;
+                }
+            }
+            for (int r = r0 + rl; r < r1; r += RL) {
+                float f[8], o[8];
+                const uint4 v = use_cache ? cache[static_cast<long long>(cached + (r - r0)) * ncol + vc]
+                                          : *reinterpret_cast<const uint4*>(src + static_cast<long long>(r) * ld + cc);
+                unpack8<T>(v, f);
+                if (p.act == ACT_SILU) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = act_silu(fmaf(f[i], a[i], b[i]));
+                } else if (p.act == ACT_NONE) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = fmaf(f[i], a[i], b[i]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = apply_act(fmaf(f[i], a[i], b[i]), p.act);
+                }
+                *reinterpret_cast<uint4*>(y + static_cast<long long>(r) * C + c) = pack8<T>(o);
+            }
+        }
+        cached += r1 - r0;
+    }
+}
+
 // ---- LayerNorm: one warp per row, row held in registers -----------------------------------------
 template <typename T, int MAXV>
 __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x, const T* __restrict__ gamma,
@@ -326,6 +547,35 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
     const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
     AB_REQUIRE(smem <= 48 * 1024, "channel count too large for the stats kernel");
+    static const bool fused_on = [] { const char* e = getenv("AB_GN_FUSED"); return !(e && e[0] == '0'); }();
+    if (fused_on) {
+        const int n_sm = ab_sm_count();
+        if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_fused_kernel<__half>), 200 * 1024)) return -1;
+        if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_fused_kernel<__nv_bfloat16>), 200 * 1024)) return -1;
+        const int total_items = a->n * GN_SHARDS * p.sub;
+        const int grid_f = total_items < n_sm ? total_items : n_sm;
+        const int items_per_cta = (total_items + grid_f - 1) / grid_f;
+        const int max_item_rows = ((a->hw + GN_SHARDS - 1) / GN_SHARDS + p.sub - 1) / p.sub + 1;
+        const long long need_rows = static_cast<long long>(items_per_cta) * max_item_rows;
+        const long long cap_rows = (200LL * 1024 - static_cast<long long>(smem)) / (static_cast<long long>(C) * 2);
+        const int cache_rows = need_rows <= cap_rows ? static_cast<int>(need_rows) : 0;
+        const size_t smem_f = smem + static_cast<size_t>(cache_rows) * C * 2;
+        unsigned int* bar = p.counters + a->n;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(grid_f);
+        cfg.blockDim = dim3(GN_THREADS);
+        cfg.dynamicSmemBytes = smem_f;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeCooperative;
+        attr[0].val.cooperative = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (a->dtype == AB_BF16) AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_fused_kernel<__nv_bfloat16>, p, bar, cache_rows));
+        else AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_fused_kernel<__half>, p, bar, cache_rows));
+        ab_count_launch(1);
+        return 0;
+    }
     dim3 grid(p.sub, GN_SHARDS, a->n);
     const int apply_cols = ncol < GN_THREADS ? ncol : GN_THREADS;
     const int apply_rows = (GN_THREADS / apply_cols) * GN_APPLY_ROWS;

@@ -1,9 +1,13 @@
 // Library-wide state: last error text, launch counter, version.
 #include <stdlib.h>
 
+#include <cuda_runtime.h>
+
 #include <atomic>
 #include <mutex>
+#include <set>
 #include <string>
+#include <utility>
 
 #include "../include/arbius_b200.h"
 
@@ -39,3 +43,32 @@ extern "C" int ab_pdl_enabled(void) {
     return v;
 }
 extern "C" void ab_set_pdl(int on) { g_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per (function, device): one process may drive several GPUs
+// (the miner's GpuPool), so remember which pairs are done instead of a single static flag per launch site.
+static std::mutex g_attr_mu;
+static std::set<std::pair<const void*, int>> g_attr_done;
+extern "C" int ab_ensure_max_smem(const void* func, int bytes) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    std::lock_guard<std::mutex> lk(g_attr_mu);
+    if (g_attr_done.count({func, dev})) return 0;
+    cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) {
+        ab_set_error(cudaGetErrorString(e));
+        return -1;
+    }
+    g_attr_done.insert({func, dev});
+    return 0;
+}
+extern "C" int ab_sm_count(void) {
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int v = cached[dev].load(std::memory_order_relaxed);
+    if (v == 0) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) v = 148;
+        cached[dev].store(v, std::memory_order_relaxed);
+    }
+    return v;
+}

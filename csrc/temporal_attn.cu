@@ -218,12 +218,8 @@ extern "C" int ab_temporal_attn(const ab_temporal_attn_args* a, void* stream_) {
     for (int s = nsrc; s < 8; ++s) { maps.q[s] = maps.q[0]; maps.k[s] = maps.k[0]; maps.v[s] = maps.v[0]; }
     constexpr int smem = 5 * TA_TILE_BYTES + 8 * 8 + 16 + 1024;
     dim3 grid((a->hw + px - 1) / px, a->heads, a->batch);
-    static bool configured = false;
-    if (!configured) {
-        AB_CHECK_CUDA(cudaFuncSetAttribute(temporal_attn_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        AB_CHECK_CUDA(cudaFuncSetAttribute(temporal_attn_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
-    }
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(temporal_attn_kernel<__half>), smem)) return -1;
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(temporal_attn_kernel<__nv_bfloat16>), smem)) return -1;
     if (a->dtype == AB_BF16) AB_CHECK_CUDA(launch_pdl(temporal_attn_kernel<__nv_bfloat16>, grid, dim3(TA_THREADS), smem, stream, maps, p));
     else AB_CHECK_CUDA(launch_pdl(temporal_attn_kernel<__half>, grid, dim3(TA_THREADS), smem, stream, maps, p));
     ab_count_launch(1);
