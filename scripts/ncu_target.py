@@ -17,7 +17,8 @@ elif what == "conv":
         for _ in range(3):
             ops.conv3x3(x, wt, b, block_n=bn, splitk=1)
 elif what == "attn":
-    q = torch.randn(2, 4096, 8, 40, device="cuda", dtype=dt); k = torch.randn_like(q); v = torch.randn_like(q)
+    shape = (2, 9216, 5, 64) if (len(sys.argv) > 2 and sys.argv[2] == "video") else (2, 4096, 8, 40)
+    q = torch.randn(*shape, device="cuda", dtype=dt); k = torch.randn_like(q); v = torch.randn_like(q)
     for _ in range(3):
         ops.flash_attn(q, k, v)
 elif what == "gn":

@@ -1,4 +1,8 @@
-"""Per-kernel time breakdown of one AnythingV3 task (CUPTI via torch.profiler; shares, not absolutes)."""
+"""Per-kernel time breakdown of one task (CUPTI via torch.profiler; shares, not absolutes).
+
+  python scripts/profile_task.py                                   # AnythingV3 512x512, 20 steps
+  python scripts/profile_task.py --model zeroscopev2xl --steps 2   # two denoise steps + VAE of the video task
+"""
 import argparse
 import json
 import re
@@ -8,19 +12,32 @@ from collections import defaultdict
 import torch
 
 sys.path.insert(0, ".")
-from arbius_b200.models.sd15.pipeline import SD15Config, SD15Pipeline  # noqa: E402
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--impl", default="native")
+    ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "zeroscopev2xl", "damo", "kandinsky2"])
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--out", default="gpurun_out/profile_task.json")
     a = ap.parse_args()
-    pipe = SD15Pipeline(SD15Config(), backend=a.impl, device="cuda", dtype=torch.float16, use_graph=False)
-    kw = dict(prompt="arbius test cat", negative_prompt="", width=a.size, height=a.size,
-              num_inference_steps=a.steps, guidance_scale=12.0, scheduler="DPMSolverMultistep")
+    if a.model == "anythingv3":
+        from arbius_b200.models.sd15.pipeline import SD15Config, SD15Pipeline
+        pipe = SD15Pipeline(SD15Config(), backend=a.impl, device="cuda", dtype=torch.float16, use_graph=False)
+        kw = dict(prompt="arbius test cat", negative_prompt="", width=a.size, height=a.size,
+                  num_inference_steps=a.steps, guidance_scale=12.0, scheduler="DPMSolverMultistep")
+    elif a.model in ("zeroscopev2xl", "damo"):
+        from arbius_b200.models.video.pipeline import TextToVideoConfig, TextToVideoPipeline
+        cfg = TextToVideoConfig.zeroscope_xl() if a.model == "zeroscopev2xl" else TextToVideoConfig.damo()
+        pipe = TextToVideoPipeline(cfg, backend=a.impl, device="cuda", dtype=torch.float16, family=a.model, use_graph=False)
+        kw = dict(prompt="a panda eating bamboo", negative_prompt="noisy", num_inference_steps=a.steps)
+    else:
+        from arbius_b200.models.kandinsky.pipeline import Kandinsky2Config, Kandinsky2Pipeline
+        cfg = Kandinsky2Config()
+        cfg.steps = a.steps
+        pipe = Kandinsky2Pipeline(cfg, backend=a.impl, device="cuda", dtype=torch.float16, use_graph=False)
+        kw = dict(prompt="arbius test cat", width=768, height=768)
     pipe.generate(seed=1, **kw)
     torch.cuda.synchronize()
     from torch.profiler import ProfilerActivity, profile
@@ -42,10 +59,10 @@ def main():
             agg[key][1] += 1
     total = sum(v[0] for v in agg.values())
     rows = sorted(([k, v[0] / 1e3, v[1]] for k, v in agg.items()), key=lambda r: -r[1])
-    print(f"total kernel time {total / 1e3:.2f} ms over {sum(r[2] for r in rows)} launches")
+    print(f"{a.model}: total kernel time {total / 1e3:.2f} ms over {sum(r[2] for r in rows)} launches")
     for k, ms, n in rows[:25]:
         print(f"{ms:9.3f} ms {100 * ms * 1e3 / total:5.1f}% {n:6d}x  avg {1e3 * ms / n:8.2f} us  {k}")
-    json.dump({"total_ms": total / 1e3, "rows": rows}, open(a.out, "w"), indent=1)
+    json.dump({"model": a.model, "total_ms": total / 1e3, "rows": rows}, open(a.out, "w"), indent=1)
 
 
 if __name__ == "__main__":
