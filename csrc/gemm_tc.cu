@@ -60,6 +60,7 @@ struct GemmParams {
     // pipeline stages) and one thread issues a bulk tensor store — full-line writes instead of 16-byte pieces
     // scattered over 32 rows per warp instruction. Off for GEGLU, split-K partials and reduce-scatter.
     int tma_store;
+    int mt;                     // 128-row M tiles per CTA (1 or 2)
     alignas(64) CUtensorMap amaps[8];
     alignas(64) CUtensorMap omap;
 };
@@ -161,16 +162,23 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
     }
 }
 
-template <int BN, int STAGES, typename T, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, (BN > 160 ? 1 : 2))
+// MT = 2: one CTA owns two M-adjacent 128-row tiles (two accumulators in TMEM) that share every weight tile it
+// loads. Shared-memory ingest per MMA cycle drops from (A + B) / t to (2A + B) / 2t: the 128 x 256 tile needs
+// ~94 B/clk at tensor peak against the ~64 B/clk an SM can take from L2 (680 cycles per K step measured, 512 ideal),
+// the 256 x 256 super-tile needs 62. Used when the problem still fills the GPU for at least two waves.
+template <int BN, int STAGES, typename T, int EPI, int MT>
+__global__ void __launch_bounds__(GEMM_THREADS, ((BN > 160 || MT > 1) ? 1 : 2))
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ GemmParams p) {
-    constexpr int A_BYTES = BM * BK * 2;
+    constexpr int A1_BYTES = BM * BK * 2;
+    constexpr int A_BYTES = MT * A1_BYTES;
     constexpr int B_BYTES = BN * BK * 2;
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    constexpr int TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+    constexpr int ACC_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+    constexpr int TMEM_COLS = MT * ACC_COLS;
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "UMMA N for M=128; epilogue reads 32-column chunks");
     static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment");
+    static_assert(MT * (BN / 32) * BM * 64 <= STAGES * STAGE_BYTES, "output staging boxes reuse the pipeline stages");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -178,7 +186,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* acc_bar = empty_bar + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
-    float* sbias = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot) + 4 + 15) & ~uintptr_t(15));  // [BN]
+    float* sbias = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot) + 4 + 15) & ~uintptr_t(15));  // [MT][BN]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -186,18 +194,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     long long* dbg = p.dbg ? p.dbg + 8LL * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
 
     // ---- tile coordinates -------------------------------------------------------------------
-    const int tile_m = blockIdx.x;
     const int n0 = blockIdx.y * BN;
-    int i0 = 0, h0 = 0, w0 = 0, m0 = 0;
-    if (p.conv) {
-        const int tw = tile_m % p.tiles_w;
-        const int th = (tile_m / p.tiles_w) % p.tiles_h;
-        const int ti = tile_m / (p.tiles_w * p.tiles_h);
-        w0 = tw << p.bw_log2;
-        h0 = th << p.bh_log2;
-        i0 = ti << (7 - p.bw_log2 - p.bh_log2);
-    } else {
-        m0 = tile_m * BM;
+    // sub-tile s of this CTA is M tile blockIdx.x * MT + s
+    int tile_ms[MT], i0s[MT], h0s[MT], w0s[MT], m0s[MT];
+#pragma unroll
+    for (int s = 0; s < MT; ++s) {
+        const int tm = blockIdx.x * MT + s;
+        tile_ms[s] = tm;
+        i0s[s] = h0s[s] = w0s[s] = m0s[s] = 0;
+        if (p.conv) {
+            const int tw = tm % p.tiles_w;
+            const int th = (tm / p.tiles_w) % p.tiles_h;
+            const int ti = tm / (p.tiles_w * p.tiles_h);
+            w0s[s] = tw << p.bw_log2;
+            h0s[s] = th << p.bh_log2;
+            i0s[s] = ti << (7 - p.bw_log2 - p.bh_log2);
+        } else {
+            m0s[s] = tm * BM;
+        }
     }
     const int chunks_per_tap = p.k1_chunks + p.k2_chunks;
     const int total_chunks = p.taps * chunks_per_tap;
@@ -241,17 +255,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const bool second = cc >= p.k1_chunks;
                 const CUtensorMap* ma = second ? &tmA2 : &tmA;
                 const int c0 = (second ? cc - p.k1_chunks : cc) * BK;
-                if (p.conv) {
-                    // conv == 1: 3x3 taps; conv == 2: 3x1 taps along H only (temporal Conv3d (3,1,1) on [B, F, HW, C])
-                    const int dh = p.conv == 2 ? tap - 1 : tap / 3 - 1;
-                    const int dw = p.conv == 2 ? 0 : tap % 3 - 1;
-                    tma_load_4d(sa, ma, &full_bar[stage], c0, w0 + dw, h0 + dh, i0);
-                } else {
-                    if (p.nsrc > 1) {
-                        const int src = tile_m / p.tiles_per_src;
-                        tma_load_2d(sa, &p.amaps[src], &full_bar[stage], c0, (tile_m - src * p.tiles_per_src) * BM);
+#pragma unroll
+                for (int s = 0; s < MT; ++s) {
+                    uint8_t* sas = sa + s * A1_BYTES;
+                    if (p.conv) {
+                        // conv == 1: 3x3 taps; conv == 2: 3x1 taps along H only (temporal Conv3d (3,1,1) on [B, F, HW, C])
+                        const int dh = p.conv == 2 ? tap - 1 : tap / 3 - 1;
+                        const int dw = p.conv == 2 ? 0 : tap % 3 - 1;
+                        tma_load_4d(sas, ma, &full_bar[stage], c0, w0s[s] + dw, h0s[s] + dh, i0s[s]);
                     } else {
-                        tma_load_2d(sa, ma, &full_bar[stage], c0, m0);
+                        if (p.nsrc > 1) {
+                            const int src = tile_ms[s] / p.tiles_per_src;
+                            tma_load_2d(sas, &p.amaps[src], &full_bar[stage], c0, (tile_ms[s] - src * p.tiles_per_src) * BM);
+                        } else {
+                            tma_load_2d(sas, ma, &full_bar[stage], c0, m0s[s]);
+                        }
                     }
                 }
                 tma_load_2d(sb, &tmB, &full_bar[stage], kc * BK, n0);
@@ -272,9 +290,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const uint32_t sb = sa + A_BYTES;
 #pragma unroll
                 for (int k = 0; k < BK / UK; ++k) {
-                    const uint64_t adesc = make_smem_desc(sa + k * UK * 2, 16, 1024, kSwizzle128);
                     const uint64_t bdesc = make_smem_desc(sb + k * UK * 2, 16, 1024, kSwizzle128);
-                    umma_ss(tmem_base, adesc, bdesc, idesc, (kc > kc_begin || k > 0) ? 1u : 0u);
+#pragma unroll
+                    for (int s = 0; s < MT; ++s) {
+                        const uint64_t adesc = make_smem_desc(sa + s * A1_BYTES + k * UK * 2, 16, 1024, kSwizzle128);
+                        umma_ss(tmem_base + s * ACC_COLS, adesc, bdesc, idesc, (kc > kc_begin || k > 0) ? 1u : 0u);
+                    }
                 }
                 umma_commit(&empty_bar[stage]);   // frees this smem stage once the MMAs have read it
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -287,6 +308,42 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int q = warp & 3;                   // TMEM lane quarter this warp may read
         const int hf = (warp - 2) >> 2;           // which half of the 32-column chunks this warp handles
         const int r = q * 32 + lane;              // row inside the tile
+        // While the main loop runs, stage bias (+ row bias if a whole sub-tile shares one group) in smem.
+        bool single_group[MT];
+        const bool use_sb = p.splitk <= 1;
+#pragma unroll
+        for (int s = 0; s < MT; ++s) {
+            int tile_grp;
+            if (p.conv) { single_group[s] = (p.bw_log2 + p.bh_log2) == 7; tile_grp = i0s[s]; }
+            else if (p.rows_per_group > 0) {
+                const long long last = min(static_cast<long long>(m0s[s]) + BM - 1, static_cast<long long>(p.M) - 1);
+                tile_grp = m0s[s] / p.rows_per_group;
+                single_group[s] = (last / p.rows_per_group) == tile_grp;
+            } else { single_group[s] = true; tile_grp = 0; }
+            if (use_sb) {
+                const T* bias = reinterpret_cast<const T*>(p.bias);
+                const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
+                for (int n = threadIdx.x - 64; n < BN; n += GEMM_THREADS - 64) {
+                    float b = 0.f;
+                    if (n0 + n < p.N) {
+                        if (bias) b = DT<T>::to_f(bias[n0 + n]);
+                        if (rowbias && single_group[s])
+                            b += DT<T>::to_f(rowbias[static_cast<long long>(tile_grp) * p.ldrb + n0 + n]);
+                    }
+                    sbias[s * BN + n] = b;
+                }
+            }
+        }
+        if (use_sb) asm volatile("bar.sync 1, 256;\n" ::: "memory");
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
+        if (dbg && threadIdx.x == 64) dbg[3] = clock64() - t_start;   // accumulator ready
+#pragma unroll
+        for (int s = 0; s < MT; ++s) {
+        const int w0 = w0s[s], h0 = h0s[s], i0 = i0s[s], m0 = m0s[s];
+        const bool rowbias_global = !single_group[s];
+        float* const sbias_s = sbias + s * BN;
+        uint8_t* const stage_base = smem + s * ((BN / 32) * BM * 64);
         long long out_row;
         int grp;
         bool row_ok;
@@ -303,34 +360,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             row_ok = out_row < p.M;
             grp = p.rows_per_group > 0 ? static_cast<int>(out_row / p.rows_per_group) : 0;
         }
-        // While the main loop runs, stage bias (+ row bias if the whole tile shares one group) in smem.
-        bool single_group;
-        int tile_grp;
-        if (p.conv) { single_group = (p.bw_log2 + p.bh_log2) == 7; tile_grp = i0; }
-        else if (p.rows_per_group > 0) {
-            const long long last = min(static_cast<long long>(m0) + BM - 1, static_cast<long long>(p.M) - 1);
-            tile_grp = m0 / p.rows_per_group;
-            single_group = (last / p.rows_per_group) == tile_grp;
-        } else { single_group = true; tile_grp = 0; }
-        const bool use_sb = p.splitk <= 1;
-        if (use_sb) {
-            const T* bias = reinterpret_cast<const T*>(p.bias);
-            const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
-            for (int n = threadIdx.x - 64; n < BN; n += GEMM_THREADS - 64) {
-                float b = 0.f;
-                if (n0 + n < p.N) {
-                    if (bias) b = DT<T>::to_f(bias[n0 + n]);
-                    if (rowbias && single_group) b += DT<T>::to_f(rowbias[static_cast<long long>(tile_grp) * p.ldrb + n0 + n]);
-                }
-                sbias[n] = b;
-            }
-            asm volatile("bar.sync 1, 256;\n" ::: "memory");
-        }
-        const bool rowbias_global = !single_group;
-        mbar_wait(acc_bar, 0);
-        tc_fence_after();
-        if (dbg && threadIdx.x == 64) dbg[3] = clock64() - t_start;   // accumulator ready
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + s * ACC_COLS;
         // Two warps share each TMEM lane quarter and take alternate 32-column chunks; the tcgen05.ld of a warp's
         // next chunk is in flight while it converts and stores the current one.
         constexpr int NCHUNK = BN / 32;
@@ -349,12 +379,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int n_base = n0 + c * 32;
             if (p.tma_store) {
                 if (n_base >= p.N) continue;                           // warp-uniform: the whole box is out of range
-                uint8_t* box = smem + c * (BM * 64);
+                uint8_t* box = stage_base + c * (BM * 64);
                 if (row_ok) {
                     float v[32];
 #pragma unroll
                     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
-                    epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias + c * 32, rowbias_global, box + r * 64,
+                    epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias_s + c * 32, rowbias_global, box + r * 64,
                                              (r >> 1) & 3);
                 }
                 fence_proxy_async();
@@ -379,10 +409,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         if (n_base + 4 * g < p.N)
                             *reinterpret_cast<float4*>(ws + 4 * g) = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
                 } else {
-                    epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias + c * 32, rowbias_global);
+                    epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias_s + c * 32, rowbias_global);
                 }
             }
         }
+        }   // sub-tiles
         if (p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
     }
 
@@ -424,7 +455,11 @@ __global__ void splitk_reduce_kernel(const GemmParams p) {
 
 // ---------------------------------------------------------------------------------------------
 // host side
+// This file is compiled twice (build.sh compiles the .cu files in parallel): as is, it holds the host entry points
+// and the fp16 kernels; gemm_tc_bf16.cu includes it with AB_GEMM_BF16_TU defined and contributes only the bf16
+// main-kernel instantiations behind ab_gemm_main_bf16() — ~110 large kernels are too slow for one nvcc process.
 // ---------------------------------------------------------------------------------------------
+#ifndef AB_GEMM_BF16_TU
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -468,6 +503,9 @@ extern "C" int ab_make_tensor_map(CUtensorMap* out, int dtype, int rank, const v
     }
     return 0;
 }
+namespace ab {
+#endif  // !AB_GEMM_BF16_TU
+}  // namespace ab
 
 namespace ab {
 
@@ -504,14 +542,27 @@ static int auto_block_n(int M_tiles, int N, bool geglu) {
     return best;
 }
 
+template <int BN, int STAGES, typename T, int EPI, int MT>
+static int launch_gemm_mt(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
+                          dim3 grid, cudaStream_t stream) {
+    constexpr int smem = STAGES * (MT * BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 32 + MT * BN * 4 + 1024;
+    static_assert(smem <= 227 * 1024, "stage count does not fit shared memory");
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, STAGES, T, EPI, MT>), smem)) return -1;
+    AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI, MT>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
+    ab_count_launch(1);
+    return 0;
+}
+
+// STAGES is the depth for one 128-row tile per CTA; the two-tile variant exists for BN = 256 only (three 64 KB stages).
+// At BN <= 160 two co-resident CTAs already overlap each other's epilogue and loads: the ZeroScope convs measured
+// 1137-1236 TFLOP/s with one tile per CTA and 1121-1238 with two, so those widths keep one.
 template <int BN, int STAGES, typename T, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
                        dim3 grid, cudaStream_t stream) {
-    constexpr int smem = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 32 + BN * 4 + 1024;
-    if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, STAGES, T, EPI>), smem)) return -1;
-    AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
-    ab_count_launch(1);
-    return 0;
+    if constexpr (BN == 256) {
+        if (p.mt == 2) return launch_gemm_mt<BN, 3, T, EPI, 2>(tmA, tmA2, tmB, p, grid, stream);
+    }
+    return launch_gemm_mt<BN, STAGES, T, EPI, 1>(tmA, tmA2, tmB, p, grid, stream);
 }
 
 template <typename T, int EPI>
@@ -528,7 +579,30 @@ static int dispatch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmA2, 
     }
 }
 
+template <typename T>
+static int gemm_main_t(int main_epi, int bn, const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                       const GemmParams& p, dim3 grid, cudaStream_t stream) {
+    switch (main_epi) {
+        case EPI_NONE: return dispatch_bn<T, EPI_NONE>(bn, tmA, tmA2, tmB, p, grid, stream);
+        case EPI_SILU: return dispatch_bn<T, EPI_SILU>(bn, tmA, tmA2, tmB, p, grid, stream);
+        case EPI_GELU: return dispatch_bn<T, EPI_GELU>(bn, tmA, tmA2, tmB, p, grid, stream);
+        case EPI_QGELU: return dispatch_bn<T, EPI_QGELU>(bn, tmA, tmA2, tmB, p, grid, stream);
+        case EPI_GEGLU: return dispatch_bn<T, EPI_GEGLU>(bn, tmA, tmA2, tmB, p, grid, stream);
+        default: return dispatch_bn<T, EPI_ANY>(bn, tmA, tmA2, tmB, p, grid, stream);
+    }
+}
+
 }  // namespace ab
+
+#ifdef AB_GEMM_BF16_TU
+extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, const CUtensorMap* tmA2, const CUtensorMap* tmB,
+                                 const void* params, unsigned gx, unsigned gy, unsigned gz, void* stream) {
+    return ab::gemm_main_t<__nv_bfloat16>(main_epi, bn, *tmA, *tmA2, *tmB, *reinterpret_cast<const ab::GemmParams*>(params),
+                                          dim3(gx, gy, gz), reinterpret_cast<cudaStream_t>(stream));
+}
+#else
+extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, const CUtensorMap* tmA2, const CUtensorMap* tmB,
+                                 const void* params, unsigned gx, unsigned gy, unsigned gz, void* stream);
 
 static long long* g_gemm_dbg = nullptr;
 // Profiling aid: point at a device buffer of >= 8 * grid_size int64 to receive per-CTA phase cycle counts.
@@ -681,7 +755,13 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         p.tma_store = 1;
     }
 
-    dim3 grid(tiles_m, (a->N + bn - 1) / bn, grid_z);
+    static const bool mt_on = [] { const char* e = getenv("AB_GEMM_MT2"); return !(e && e[0] == '0'); }();
+    const int n_tiles = (a->N + bn - 1) / bn;
+    // two tiles per CTA: only for long main loops (the doubled epilogue is serial behind them: 512x512x128->128 with
+    // 18 K steps got 20 % slower) on problems that still give every SM two waves
+    p.mt = (mt_on && !ag && bn == 256 && tiles_m % 2 == 0 && p.chunks_per_split >= 24 &&
+            static_cast<long long>(tiles_m / 2) * n_tiles * grid_z >= 2LL * ab_sm_count()) ? 2 : 1;
+    dim3 grid(tiles_m / p.mt, n_tiles, grid_z);
     int epi = a->geglu ? EPI_GEGLU
             : a->act == ACT_NONE ? EPI_NONE
             : a->act == ACT_SILU ? EPI_SILU
@@ -690,17 +770,8 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     const int main_epi = splitk > 1 ? EPI_NONE : epi;     // with split-K the main kernel only stores fp32 partials
     int rc = 0;
     if (phase != 2) {
-#define AB_GEMM_EPI(T)                                                                                     \
-    switch (main_epi) {                                                                                    \
-        case EPI_NONE: rc = dispatch_bn<T, EPI_NONE>(bn, tmA, tmA2, tmB, p, grid, stream); break;          \
-        case EPI_SILU: rc = dispatch_bn<T, EPI_SILU>(bn, tmA, tmA2, tmB, p, grid, stream); break;          \
-        case EPI_GELU: rc = dispatch_bn<T, EPI_GELU>(bn, tmA, tmA2, tmB, p, grid, stream); break;          \
-        case EPI_QGELU: rc = dispatch_bn<T, EPI_QGELU>(bn, tmA, tmA2, tmB, p, grid, stream); break;        \
-        case EPI_GEGLU: rc = dispatch_bn<T, EPI_GEGLU>(bn, tmA, tmA2, tmB, p, grid, stream); break;        \
-        default: rc = dispatch_bn<T, EPI_ANY>(bn, tmA, tmA2, tmB, p, grid, stream); break;                 \
-    }
-    if (a->dtype == AB_BF16) { AB_GEMM_EPI(__nv_bfloat16) } else { AB_GEMM_EPI(__half) }
-#undef AB_GEMM_EPI
+        if (a->dtype == AB_BF16) rc = ab_gemm_main_bf16(main_epi, bn, &tmA, &tmA2, &tmB, &p, grid.x, grid.y, grid.z, stream_);
+        else rc = gemm_main_t<__half>(main_epi, bn, tmA, tmA2, tmB, p, grid, stream);
     }
     if (rc) return rc;
     if (splitk > 1 && phase != 1) {
@@ -725,3 +796,5 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     }
     return 0;
 }
+
+#endif  // !AB_GEMM_BF16_TU
