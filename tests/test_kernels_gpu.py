@@ -253,3 +253,54 @@ def test_flash_attn_fused_qkv_views_and_large_logits(dt):
     # logits with a huge dynamic range exercise the lazy-rescale path
     q2 = q * 6
     _close(ops.flash_attn(q2, k, v), _attn_ref(q2, k, v), dt)
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_gemm_two_tiles_per_cta_and_tma_store_edges(dt):
+    """Large BN=256 problems take the two-M-tiles-per-CTA kernel; odd widths and sliced outputs go through the
+    TMA-store epilogue (clipped boxes) or its direct-store fallback."""
+    from arbius_b200 import ops
+    x = torch.randn(16384, 1536, device="cuda", dtype=dt)
+    w = torch.randn(2048, 1536, device="cuda", dtype=dt) / 1536 ** 0.5
+    b = torch.randn(2048, device="cuda", dtype=dt)
+    res = torch.randn(16384, 2048, device="cuda", dtype=dt)
+    y = ops.gemm(x, w, b, residual=res, act="silu", block_n=256, splitk=1)
+    ref = F.silu(x.float() @ w.float().t() + b.float()) + res.float()
+    _close(y, ref, dt)
+    # conv through the same path: 16 images of 64x64, 256 -> 512 channels
+    xi = torch.randn(16, 64, 64, 256, device="cuda", dtype=dt)
+    wc = torch.randn(512, 256, 3, 3, device="cuda", dtype=dt) / (9 * 256) ** 0.5
+    yc = ops.conv3x3(xi, ops.pack_conv_weight(wc), None, block_n=256, splitk=1)
+    refc = F.conv2d(xi.float().permute(0, 3, 1, 2), wc.float(), padding=1).permute(0, 2, 3, 1)
+    _close(yc, refc, dt)
+    # N = 72 (last 32-column box clipped to 8 columns), M = 300 (last row box clipped), output a column slice
+    x2 = torch.randn(300, 200, device="cuda", dtype=dt)
+    w2 = torch.randn(72, 200, device="cuda", dtype=dt) / 200 ** 0.5
+    wide = torch.zeros(300, 160, device="cuda", dtype=dt)
+    ops.gemm(x2, w2, None, out=wide[:, 80:152], splitk=1)
+    _close(wide[:, 80:152], x2.float() @ w2.float().t(), dt)
+    assert (wide[:, :80] == 0).all() and (wide[:, 152:] == 0).all(), "TMA store wrote outside its column slice"
+
+
+def test_groupnorm_fused_kernel_matches_two_kernel_path_bitwise():
+    """ab_groupnorm (one cooperative launch when the rows fit shared memory) and ab_groupnorm_static (always the
+    two-kernel path) share the canonical decomposition: same bits."""
+    import ctypes as C
+    from arbius_b200 import ops
+    from arbius_b200.ops import native
+    from arbius_b200.ops.native import ACT, GroupNormArgs
+    lib = native.load()
+    for (n, hw, c) in [(2, 4096, 320), (2, 1024, 640), (1, 256, 1280)]:
+        x = torch.randn(n, hw, c, device="cuda", dtype=torch.float16) * 3 - 1
+        g = torch.randn(c, device="cuda", dtype=torch.float16)
+        b = torch.randn(c, device="cuda", dtype=torch.float16)
+        y = ops.groupnorm(x, g, b, 32, 1e-5, "silu")
+        y2 = torch.empty_like(x)
+        a = GroupNormArgs()
+        a.x, a.y, a.gamma, a.beta = x.data_ptr(), y2.data_ptr(), g.data_ptr(), b.data_ptr()
+        a.n, a.hw, a.c1, a.c2, a.groups, a.eps, a.act, a.dtype = n, hw, c, 0, 32, 1e-5, ACT["silu"], 0
+        lib.ab_groupnorm_static.restype = C.c_int
+        lib.ab_groupnorm_static.argtypes = [C.POINTER(GroupNormArgs), C.c_void_p]
+        native.check(lib.ab_groupnorm_static(C.byref(a), native.stream_ptr()), "ab_groupnorm_static")
+        torch.cuda.synchronize()
+        assert torch.equal(y, y2), (n, hw, c)
