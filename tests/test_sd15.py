@@ -70,6 +70,11 @@ def test_eager_pipeline_cpu_is_deterministic():
     png = pipe.predict({"prompt": "x", "negative_prompt": "", "width": 64, "height": 64, "num_inference_steps": 2,
                         "guidance_scale": 7, "scheduler": "K_EULER_ANCESTRAL", "seed": 5})
     assert png[:8] == b"\x89PNG\r\n\x1a\n"
+    # the queue API returns the same bytes, in order
+    inputs = [{"prompt": "x", "negative_prompt": "", "width": 64, "height": 64, "num_inference_steps": 2,
+               "guidance_scale": 7, "scheduler": "K_EULER_ANCESTRAL", "seed": s} for s in (5, 6, 5)]
+    many = pipe.predict_many(inputs)
+    assert many[0] == png and many[2] == png and many[1] != png
 
 
 # ------------------------------------------------------------------ GPU
