@@ -18,11 +18,14 @@ namespace ab {
 constexpr int GN_SHARDS = 8;
 constexpr int GN_MAX_SUB = 32;
 constexpr int GN_THREADS = 512;
+constexpr int GN_APPLY_THREADS = 256;   // apply is elementwise: smaller blocks, two or more per SM, so loads of one overlap stores of another
 constexpr int GN_MAX_GROUPS = 64;
 
 __host__ __device__ inline int gn_sub_blocks(int hw) {
     int rows = (hw + GN_SHARDS - 1) / GN_SHARDS;
-    int sub = (rows + 63) / 64;
+    // 64 rows per block keeps small maps parallel; from 8192 positions up, 128 rows amortise the per-block
+    // reduction and ticket (a function of HW only: the partition is part of the canonical reduction order)
+    int sub = hw >= 8192 ? (rows + 127) / 128 : (rows + 63) / 64;
     return sub < 1 ? 1 : (sub > GN_MAX_SUB ? GN_MAX_SUB : sub);
 }
 
@@ -56,6 +59,36 @@ __device__ __forceinline__ GnMoments gn_merge(const GnMoments a, const GnMoments
     r.mean = fmaf(delta, w, a.mean);
     r.m2 = a.m2 + b.m2 + delta * delta * a.cnt * w;
     return r;
+}
+
+// Per-block group moments from the per-thread column sums in shared memory ([RL][C] sums and squares): sixteen lanes
+// per group, lane j takes the values j, j+16, ... of the group's RL*cpg entries (index rl*cpg + k) and a fixed xor tree
+// combines them — the same order in every kernel that calls this, so the two-kernel and the fused path agree bitwise.
+__device__ __forceinline__ void gn_block_moments(const float* s_sum, const float* s_sq, int RL, int C, int cpg, int groups,
+                                                 int rows, float4* dst) {
+    const int j = threadIdx.x & 15;
+    const int nval = RL * cpg;
+    for (int g = threadIdx.x >> 4; g < ((groups + 1) & ~1); g += GN_THREADS >> 4) {
+        float ds = 0.f, dq = 0.f;
+        if (g < groups) {
+            for (int idx = j; idx < nval; idx += 16) {
+                const int rl = idx / cpg, k = idx - rl * cpg;
+                ds += s_sum[rl * C + g * cpg + k];
+                dq += s_sq[rl * C + g * cpg + k];
+            }
+        }
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            ds += __shfl_xor_sync(0xffffffffu, ds, o);
+            dq += __shfl_xor_sync(0xffffffffu, dq, o);
+        }
+        if (j == 0 && g < groups) {
+            const float cnt = static_cast<float>(rows) * cpg;
+            const float mean = cnt > 0.f ? ds / cnt : 0.f;
+            const float m2 = fmaxf(dq - ds * mean, 0.f);
+            dst[g] = make_float4(cnt, mean, m2, 0.f);
+        }
+    }
 }
 
 template <typename T>
@@ -129,17 +162,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
         }
     }
     __syncthreads();
-    if (threadIdx.x < p.groups) {
-        const int g = threadIdx.x;
-        float ds = 0.f, dq = 0.f;
-        for (int rl = 0; rl < RL; ++rl)
-            for (int c = g * cpg; c < (g + 1) * cpg; ++c) { ds += s_sum[rl * C + c]; dq += s_sq[rl * C + c]; }
-        const float cnt = static_cast<float>(r1 - r0) * cpg;
-        const float mean = cnt > 0.f ? ds / cnt : 0.f;
-        const float m2 = fmaxf(dq - ds * mean, 0.f);
-        p.partials[((static_cast<long long>(n) * GN_SHARDS + shard) * p.sub + sub) * p.groups + g] =
-            make_float4(cnt, mean, m2, 0.f);
-    }
+    gn_block_moments(s_sum, s_sq, RL, C, cpg, p.groups, r1 - r0,
+                     p.partials + ((static_cast<long long>(n) * GN_SHARDS + shard) * p.sub + sub) * p.groups);
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -177,13 +201,13 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
 // the affine is folded once into (a, b) and every row costs one 16-byte load, 8 FMAs and one 16-byte store.
 constexpr int GN_APPLY_ROWS = 8;   // rows per thread
 template <typename T>
-__global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const GnParams p) {
+__global__ void __launch_bounds__(GN_APPLY_THREADS, 2) gn_apply_kernel(const GnParams p) {
     const int C = p.c1 + p.c2;
     const int ncol = C / 8;
     const int cpg = C / p.groups;
     const int n = blockIdx.y;
-    const int cols = ncol < GN_THREADS ? ncol : GN_THREADS;
-    const int RL = GN_THREADS / cols;
+    const int cols = ncol < GN_APPLY_THREADS ? ncol : GN_APPLY_THREADS;
+    const int RL = GN_APPLY_THREADS / cols;
     const int passes = (ncol + cols - 1) / cols;
     const int rl = threadIdx.x / cols;
     pdl_wait();
@@ -367,17 +391,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_fused_kernel(const GnParams p, 
             }
         }
         __syncthreads();
-        if (threadIdx.x < p.groups) {
-            const int g = threadIdx.x;
-            float ds = 0.f, dq = 0.f;
-            for (int rl = 0; rl < RL; ++rl)
-                for (int c = g * cpg; c < (g + 1) * cpg; ++c) { ds += s_sum[rl * C + c]; dq += s_sq[rl * C + c]; }
-            const float cnt = static_cast<float>(r1 - r0) * cpg;
-            const float mean = cnt > 0.f ? ds / cnt : 0.f;
-            const float m2 = fmaxf(dq - ds * mean, 0.f);
-            p.partials[static_cast<long long>(item) * p.groups + g] = make_float4(cnt, mean, m2, 0.f);
-            __threadfence();
-        }
+        gn_block_moments(s_sum, s_sq, RL, C, cpg, p.groups, r1 - r0, p.partials + static_cast<long long>(item) * p.groups);
+        __threadfence();
         __syncthreads();
         cached += r1 - r0;
     }
@@ -590,15 +605,15 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
         return 0;
     }
     dim3 grid(p.sub, GN_SHARDS, a->n);
-    const int apply_cols = ncol < GN_THREADS ? ncol : GN_THREADS;
-    const int apply_rows = (GN_THREADS / apply_cols) * GN_APPLY_ROWS;
+    const int apply_cols = ncol < GN_APPLY_THREADS ? ncol : GN_APPLY_THREADS;
+    const int apply_rows = (GN_APPLY_THREADS / apply_cols) * GN_APPLY_ROWS;
     dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
         AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__nv_bfloat16>, grid, dim3(GN_THREADS), smem, stream, p));
-        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_THREADS), 0, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     } else {
         AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__half>, grid, dim3(GN_THREADS), smem, stream, p));
-        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_THREADS), 0, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     }
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(2);
@@ -689,15 +704,15 @@ extern "C" int ab_groupnorm_static(const ab_groupnorm_args* a, void* stream_) {
     // the block tickets must start at zero whatever an earlier (possibly failed) call left behind
     AB_CHECK_CUDA(cudaMemsetAsync(ws, 0, kStaticCountersBytes, stream));
     dim3 grid(p.sub, GN_SHARDS, a->n);
-    const int apply_cols = ncol < GN_THREADS ? ncol : GN_THREADS;
-    const int apply_rows = (GN_THREADS / apply_cols) * GN_APPLY_ROWS;
+    const int apply_cols = ncol < GN_APPLY_THREADS ? ncol : GN_APPLY_THREADS;
+    const int apply_rows = (GN_APPLY_THREADS / apply_cols) * GN_APPLY_ROWS;
     dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
         AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__nv_bfloat16>, grid, dim3(GN_THREADS), smem, stream, p));
-        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_THREADS), 0, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     } else {
         AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__half>, grid, dim3(GN_THREADS), smem, stream, p));
-        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_THREADS), 0, stream, p));
+        AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     }
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(2);

@@ -26,6 +26,12 @@ constexpr int TA_TILE_BYTES = 128 * 128;
 
 struct TaMaps { CUtensorMap q[8], k[8], v[8]; };
 
+__device__ __forceinline__ float ex2_approx_ta(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 struct TaParams {
     void* out[8];            // per-source output buffers [B, F_s, HW, heads*D] (row stride o_ls elements)
     int batch, heads, frames, frames_per_src, nsrc, hw, px, head_dim;
@@ -33,16 +39,21 @@ struct TaParams {
     float scale_log2;
 };
 
-template <typename T>
-__global__ void __launch_bounds__(TA_THREADS, 2)
+// PM (pixel-major rows): row = pixel * F + frame, so a row's valid keys are the contiguous columns of its own pixel
+// (two compares per score instead of an integer modulo) — needs F_s % 8 == 0 so every per-pixel TMA box starts on a
+// 1024-byte swizzle atom. Otherwise rows stay frame-major (one box per source) with the modulo mask.
+// Shared memory: P aliases Q|K (both are dead once S is complete) and O aliases S's first columns (S is dead once P
+// is written): 48 KB + 128 TMEM columns per CTA, four CTAs per SM hide each other's load -> MMA -> softmax chain.
+template <typename T, bool PM>
+__global__ void __launch_bounds__(TA_THREADS, 4)
 temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
     uint8_t* sK = sQ + TA_TILE_BYTES;
     uint8_t* sV = sK + TA_TILE_BYTES;
-    uint8_t* sP = sV + TA_TILE_BYTES;                      // 2 x 16 KB (128 keys = two 64-wide K chunks)
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * TA_TILE_BYTES);
+    uint8_t* sP = sQ;                                      // 2 x 16 KB (128 keys = two 64-wide K chunks), over Q|K
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + TA_TILE_BYTES);
     uint64_t* ld_full = bars;
     uint64_t* s_full = bars + 1;
     uint64_t* p_full = bars + 2;
@@ -70,7 +81,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
         mbar_init(ld_full, 1); mbar_init(s_full, 1); mbar_init(p_full, 128); mbar_init(o_full, 1);
         fence_barrier_init();
     }
-    if (warp == 0) tmem_alloc<256>(tmem_slot);
+    if (warp == 0) tmem_alloc<128>(tmem_slot);
     fence_proxy_async();                                   // the zero fill above must be visible to the MMA
     tc_fence_before();
     __syncthreads();
@@ -83,10 +94,19 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
         if (lane == 0) {
             mbar_expect_tx(ld_full, 3u * static_cast<uint32_t>(R) * 128u);
             for (int s = 0; s < p.nsrc; ++s) {
-                const int off = s * rows_per_src * 128;
-                tma_load_5d(sQ + off, &maps.q[s], ld_full, 0, h, pix0, 0, b);
-                tma_load_5d(sK + off, &maps.k[s], ld_full, 0, h, pix0, 0, b);
-                tma_load_5d(sV + off, &maps.v[s], ld_full, 0, h, pix0, 0, b);
+                if constexpr (PM) {
+                    for (int px = 0; px < p.px; ++px) {       // box = (D, 1 head, 1 pixel, F_s frames)
+                        const int off = (px * p.frames + s * p.frames_per_src) * 128;
+                        tma_load_5d(sQ + off, &maps.q[s], ld_full, 0, h, pix0 + px, 0, b);
+                        tma_load_5d(sK + off, &maps.k[s], ld_full, 0, h, pix0 + px, 0, b);
+                        tma_load_5d(sV + off, &maps.v[s], ld_full, 0, h, pix0 + px, 0, b);
+                    }
+                } else {
+                    const int off = s * rows_per_src * 128;
+                    tma_load_5d(sQ + off, &maps.q[s], ld_full, 0, h, pix0, 0, b);
+                    tma_load_5d(sK + off, &maps.k[s], ld_full, 0, h, pix0, 0, b);
+                    tma_load_5d(sV + off, &maps.v[s], ld_full, 0, h, pix0, 0, b);
+                }
             }
             const uint32_t idesc_qk = make_idesc_f16(128, 128, DT<T>::kBf16, false, false);
             const uint32_t idesc_pv = make_idesc_f16(128, DP, DT<T>::kBf16, false, true);
@@ -100,7 +120,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
             mbar_wait(p_full, 0);
             tc_fence_after();
             for (int ks = 0; ks < 8; ++ks)
-                umma_ss(tmem_base + 128u, make_smem_desc(p_addr + (ks >> 2) * TA_TILE_BYTES + (ks & 3) * 32, 16, 1024, kSwizzle128),
+                umma_ss(tmem_base, make_smem_desc(p_addr + (ks >> 2) * TA_TILE_BYTES + (ks & 3) * 32, 16, 1024, kSwizzle128),
                         make_smem_desc(v_addr + ks * 16 * 128, TA_TILE_BYTES, 1024, kSwizzle128), idesc_pv, ks > 0 ? 1u : 0u);
             umma_commit(o_full);
         }
@@ -108,7 +128,8 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
         const int qd = warp & 3;
         const int r = qd * 32 + lane;
         const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
-        const int my_pix = r % p.px;
+        const int my_pix = PM ? r / p.frames : r % p.px;
+        const int col_lo = my_pix * p.frames, col_hi = col_lo + p.frames;     // PM: this row's keys
         mbar_wait(s_full, 0);
         tc_fence_after();
         float mx = -INFINITY;
@@ -120,7 +141,8 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
                 const int col = c * 32 + i;
-                if (col < R && (col % p.px) == my_pix) mx = fmaxf(mx, __uint_as_float(raw[i]));
+                const bool mine = PM ? (col >= col_lo && col < col_hi) : (col < R && (col % p.px) == my_pix);
+                if (mine) mx = fmaxf(mx, __uint_as_float(raw[i]));
             }
         }
         mx *= p.scale_log2;
@@ -135,7 +157,8 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
                 const int col = c * 32 + i;
-                pv[i] = (col < R && (col % p.px) == my_pix) ? exp2f(fmaf(__uint_as_float(raw[i]), p.scale_log2, neg_m)) : 0.f;
+                const bool mine = PM ? (col >= col_lo && col < col_hi) : (col < R && (col % p.px) == my_pix);
+                pv[i] = mine ? ex2_approx_ta(fmaf(__uint_as_float(raw[i]), p.scale_log2, neg_m)) : 0.f;
                 l_sum += pv[i];
             }
             uint8_t* slab = sP + (c >> 1) * TA_TILE_BYTES + r * 128;
@@ -154,7 +177,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
         mbar_wait(o_full, 0);
         tc_fence_after();
         const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
-        const int f = r / p.px;
+        const int f = PM ? r % p.frames : r / p.px;
         const int pix = pix0 + my_pix;
         const bool ok = r < R && pix < p.hw;
         const int src = ok ? f / p.frames_per_src : 0;
@@ -164,7 +187,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
 #pragma unroll 1
         for (int c = 0; c < DP; c += 16) {
             uint32_t raw[16];
-            tmem_ld16(tmem_base + lane_off + 128u + c, raw);
+            tmem_ld16(tmem_base + lane_off + c, raw);
             tmem_wait_ld();
             if (ok) {
 #pragma unroll
@@ -181,7 +204,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc<256>(tmem_base);
+    if (warp == 0) tmem_dealloc<128>(tmem_base);
 }
 
 }  // namespace ab
@@ -203,6 +226,7 @@ extern "C" int ab_temporal_attn(const ab_temporal_attn_args* a, void* stream_) {
     p.head_dim = D; p.o_ls = a->out_row_stride;
     const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
     p.scale_log2 = scale * 1.4426950408889634f;
+    const bool pm = (Fs % 8 == 0);
     TaMaps maps;
     for (int s = 0; s < nsrc; ++s) {
         AB_REQUIRE(a->q[s] && a->k[s] && a->v[s] && a->out[s], "null source pointer");
@@ -210,18 +234,22 @@ extern "C" int ab_temporal_attn(const ab_temporal_attn_args* a, void* stream_) {
         const uint64_t ls = (uint64_t)a->row_stride * 2;
         uint64_t dims[5] = {(uint64_t)D, (uint64_t)a->heads, (uint64_t)a->hw, (uint64_t)Fs, (uint64_t)a->batch};
         uint64_t str[4] = {(uint64_t)D * 2, ls, ls * a->hw, ls * a->hw * Fs};
-        uint32_t box[5] = {64, 1, (uint32_t)px, (uint32_t)Fs, 1};
+        uint32_t box[5] = {64, 1, (uint32_t)(pm ? 1 : px), (uint32_t)Fs, 1};
         if (ab_make_tensor_map(&maps.q[s], a->dtype, 5, a->q[s], dims, str, box, 128)) return -1;
         if (ab_make_tensor_map(&maps.k[s], a->dtype, 5, a->k[s], dims, str, box, 128)) return -1;
         if (ab_make_tensor_map(&maps.v[s], a->dtype, 5, a->v[s], dims, str, box, 128)) return -1;
     }
     for (int s = nsrc; s < 8; ++s) { maps.q[s] = maps.q[0]; maps.k[s] = maps.k[0]; maps.v[s] = maps.v[0]; }
-    constexpr int smem = 5 * TA_TILE_BYTES + 8 * 8 + 16 + 1024;
+    constexpr int smem = 3 * TA_TILE_BYTES + 8 * 8 + 16 + 1024;
     dim3 grid((a->hw + px - 1) / px, a->heads, a->batch);
-    if (ab_ensure_max_smem(reinterpret_cast<const void*>(temporal_attn_kernel<__half>), smem)) return -1;
-    if (ab_ensure_max_smem(reinterpret_cast<const void*>(temporal_attn_kernel<__nv_bfloat16>), smem)) return -1;
-    if (a->dtype == AB_BF16) AB_CHECK_CUDA(launch_pdl(temporal_attn_kernel<__nv_bfloat16>, grid, dim3(TA_THREADS), smem, stream, maps, p));
-    else AB_CHECK_CUDA(launch_pdl(temporal_attn_kernel<__half>, grid, dim3(TA_THREADS), smem, stream, maps, p));
+#define AB_TA_LAUNCH(T, PMV)                                                                                      \
+    do {                                                                                                         \
+        if (ab_ensure_max_smem(reinterpret_cast<const void*>(temporal_attn_kernel<T, PMV>), smem)) return -1;    \
+        AB_CHECK_CUDA(launch_pdl(temporal_attn_kernel<T, PMV>, grid, dim3(TA_THREADS), smem, stream, maps, p));  \
+    } while (0)
+    if (a->dtype == AB_BF16) { if (pm) AB_TA_LAUNCH(__nv_bfloat16, true); else AB_TA_LAUNCH(__nv_bfloat16, false); }
+    else { if (pm) AB_TA_LAUNCH(__half, true); else AB_TA_LAUNCH(__half, false); }
+#undef AB_TA_LAUNCH
     ab_count_launch(1);
     return 0;
 }
