@@ -40,6 +40,7 @@ struct GnParams {
     float eps;
     int act;
     int ss;                  // row stride (elements) of scale/shift
+    int apply_nb;            // batches of GN_APPLY_ROWS rows per apply thread (amortises the affine set-up on big maps)
 };
 
 // workspace layout: counters (n * 4 B, padded to 256) | stats (n*groups*8 B, padded to 256) | partials
@@ -213,8 +214,9 @@ __global__ void __launch_bounds__(GN_APPLY_THREADS, 2) gn_apply_kernel(const GnP
     pdl_wait();
     pdl_launch_dependents();
     if (rl >= RL) return;
-    const int r_begin = blockIdx.x * (RL * GN_APPLY_ROWS);
-    const int r_end = min(p.hw, r_begin + RL * GN_APPLY_ROWS);
+    const int nb = p.apply_nb > 0 ? p.apply_nb : 1;
+    const int r_block = blockIdx.x * (RL * GN_APPLY_ROWS * nb);
+    const int r_end = min(p.hw, r_block + RL * GN_APPLY_ROWS * nb);
     const T* gamma = reinterpret_cast<const T*>(p.gamma);
     const T* beta = reinterpret_cast<const T*>(p.beta);
     const T* scale = reinterpret_cast<const T*>(p.scale);
@@ -245,6 +247,8 @@ __global__ void __launch_bounds__(GN_APPLY_THREADS, 2) gn_apply_kernel(const GnP
                 a[i] = ai; b[i] = bi;
             }
         }
+        for (int bt = 0; bt < nb; ++bt) {
+        const int r_begin = r_block + bt * RL * GN_APPLY_ROWS;
         // all of this thread's row vectors are requested before the first one is used (8 x 16 B in flight per thread)
         uint4 v[GN_APPLY_ROWS];
 #pragma unroll
@@ -270,6 +274,7 @@ __global__ void __launch_bounds__(GN_APPLY_THREADS, 2) gn_apply_kernel(const GnP
             }
             *reinterpret_cast<uint4*>(y + static_cast<long long>(r) * C + c) = pack8<T>(o);
         }
+        }   // batches
     }
 }
 
@@ -606,7 +611,8 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     }
     dim3 grid(p.sub, GN_SHARDS, a->n);
     const int apply_cols = ncol < GN_APPLY_THREADS ? ncol : GN_APPLY_THREADS;
-    const int apply_rows = (GN_APPLY_THREADS / apply_cols) * GN_APPLY_ROWS;
+    p.apply_nb = static_cast<long long>(a->n) * a->hw >= 65536 ? 4 : 1;   // elementwise: free to depend on n
+    const int apply_rows = (GN_APPLY_THREADS / apply_cols) * GN_APPLY_ROWS * p.apply_nb;
     dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
         AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__nv_bfloat16>, grid, dim3(GN_THREADS), smem, stream, p));
@@ -705,7 +711,8 @@ extern "C" int ab_groupnorm_static(const ab_groupnorm_args* a, void* stream_) {
     AB_CHECK_CUDA(cudaMemsetAsync(ws, 0, kStaticCountersBytes, stream));
     dim3 grid(p.sub, GN_SHARDS, a->n);
     const int apply_cols = ncol < GN_APPLY_THREADS ? ncol : GN_APPLY_THREADS;
-    const int apply_rows = (GN_APPLY_THREADS / apply_cols) * GN_APPLY_ROWS;
+    p.apply_nb = static_cast<long long>(a->n) * a->hw >= 65536 ? 4 : 1;   // elementwise: free to depend on n
+    const int apply_rows = (GN_APPLY_THREADS / apply_cols) * GN_APPLY_ROWS * p.apply_nb;
     dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
     if (a->dtype == AB_BF16) {
         AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__nv_bfloat16>, grid, dim3(GN_THREADS), smem, stream, p));
