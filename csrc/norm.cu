@@ -402,11 +402,19 @@ __global__ void __launch_bounds__(GN_THREADS) gn_fused_kernel(const GnParams p, 
         cached += r1 - r0;
     }
 
+    // the affine parameters do not depend on the statistics: fetch them before the barrier, not after it
+    const T* gamma = reinterpret_cast<const T*>(p.gamma);
+    const T* beta = reinterpret_cast<const T*>(p.beta);
+    uint4 h_gamma = make_uint4(0, 0, 0, 0), h_beta = make_uint4(0, 0, 0, 0);
+    if (passes == 1 && threadIdx.x / ncol < RL) {
+        const int c_h = (threadIdx.x % ncol) * 8;
+        if (gamma) h_gamma = __ldg(reinterpret_cast<const uint4*>(gamma + c_h));
+        if (beta) h_beta = __ldg(reinterpret_cast<const uint4*>(beta + c_h));
+    }
+
     gn_grid_barrier(bar, gridDim.x);
 
     // ---------------- phase 2 + 3: merge the image's partials in canonical order, then normalise ----------------
-    const T* gamma = reinterpret_cast<const T*>(p.gamma);
-    const T* beta = reinterpret_cast<const T*>(p.beta);
     const T* scale = reinterpret_cast<const T*>(p.scale);
     const T* shift = reinterpret_cast<const T*>(p.shift);
     int stats_n = -1;
@@ -420,9 +428,14 @@ __global__ void __launch_bounds__(GN_THREADS) gn_fused_kernel(const GnParams p, 
             for (int idx = threadIdx.x; idx < GN_SHARDS * p.groups; idx += GN_THREADS) {
                 const int sh = idx / p.groups, g = idx % p.groups;
                 GnMoments acc{0.f, 0.f, 0.f};
-                for (int sb = 0; sb < p.sub; ++sb) {
-                    const float4 q4 = __ldcg(&part[(sh * p.sub + sb) * p.groups + g]);
-                    acc = gn_merge(acc, GnMoments{q4.x, q4.y, q4.z});
+                for (int sb0 = 0; sb0 < p.sub; sb0 += 8) {           // eight L2 loads in flight, merged in index order
+                    float4 q4[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (sb0 + u < p.sub) q4[u] = __ldcg(&part[(sh * p.sub + sb0 + u) * p.groups + g]);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (sb0 + u < p.sub) acc = gn_merge(acc, GnMoments{q4[u].x, q4[u].y, q4[u].z});
                 }
                 shard_mom[sh][g] = acc;
             }
@@ -452,8 +465,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_fused_kernel(const GnParams p, 
             float a[8], b[8];
             {
                 float ga[8], be[8], sc[8], sh[8];
-                if (gamma) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
-                if (beta) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(beta + c)), be);
+                if (gamma) unpack8<T>(passes == 1 ? h_gamma : __ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
+                if (beta) unpack8<T>(passes == 1 ? h_beta : __ldg(reinterpret_cast<const uint4*>(beta + c)), be);
                 if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * p.ss + c)), sc);
                 if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * p.ss + c)), sh);
 #pragma unroll
