@@ -202,7 +202,7 @@ class Kandinsky2Pipeline:
                 torch.cuda.synchronize()
                 graph = torch.cuda.CUDAGraph()
                 n0 = ops.native.launch_count()
-                with torch.cuda.graph(graph):
+                with ops.native.graph_capture(graph):
                     self._run_native(st)
                 st["launches"] = ops.native.launch_count() - n0
                 st["graph"] = graph

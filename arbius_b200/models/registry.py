@@ -1,10 +1,36 @@
 """Template name -> predictor factory. A predictor maps the hydrated template input (+ ``seed``) to the
-bytes of the template's output file (``out-1.png`` / ``out-1.mp4``); SURVEY Appendix A.3."""
+bytes of the template's output file (``out-1.png`` / ``out-1.mp4``); SURVEY Appendix A.3.
+
+One process may own several GPUs (the miner's GpuPool runs one predictor per device on worker threads), and the native
+ops launch on the *current* device's stream: pipelines are therefore built, and every prediction runs, under a
+``torch.cuda.device`` guard for the predictor's own device.
+"""
 from __future__ import annotations
 
 from typing import Callable, Optional
 
 FAMILIES = ("anythingv3", "kandinsky2", "zeroscopev2xl", "damo", "robust_video_matting")
+
+
+def _make_pipeline(name: str, device: str, model_dir: Optional[str], tiny: bool, backend: str, dtype):
+    if name == "anythingv3":
+        from .sd15.pipeline import SD15Config, SD15Pipeline
+        return SD15Pipeline(SD15Config.tiny() if tiny else SD15Config(), backend=backend, device=device, dtype=dtype,
+                            model_dir=model_dir)
+    if name == "kandinsky2":
+        from .kandinsky.pipeline import Kandinsky2Config, Kandinsky2Pipeline
+        return Kandinsky2Pipeline(Kandinsky2Config.tiny() if tiny else Kandinsky2Config(), backend=backend,
+                                  device=device, dtype=dtype, model_dir=model_dir)
+    if name in ("zeroscopev2xl", "damo"):
+        from .video.pipeline import TextToVideoConfig, TextToVideoPipeline
+        cfg = TextToVideoConfig.tiny() if tiny else (TextToVideoConfig.zeroscope_xl() if name == "zeroscopev2xl"
+                                                      else TextToVideoConfig.damo())
+        return TextToVideoPipeline(cfg, backend=backend, device=device, dtype=dtype, model_dir=model_dir, family=name)
+    if name == "robust_video_matting":
+        from .rvm.pipeline import RvmConfig, RvmPipeline
+        return RvmPipeline(RvmConfig.tiny() if tiny else RvmConfig(), backend=backend, device=device, dtype=dtype,
+                           model_dir=model_dir)
+    raise ValueError(f"unknown model family {name!r}; choices: {FAMILIES}")
 
 
 def build_predictor(name: str, device: str = "cuda:0", model_dir: Optional[str] = None, tiny: bool = False,
@@ -13,25 +39,14 @@ def build_predictor(name: str, device: str = "cuda:0", model_dir: Optional[str] 
     dev = torch.device(device)
     backend = backend or ("native" if dev.type == "cuda" else "eager")
     dtype = dtype or (torch.float16 if dev.type == "cuda" else torch.float32)
-    if name == "anythingv3":
-        from .sd15.pipeline import SD15Config, SD15Pipeline
-        pipe = SD15Pipeline(SD15Config.tiny() if tiny else SD15Config(), backend=backend, device=device, dtype=dtype,
-                            model_dir=model_dir)
-        return pipe.predict
-    if name == "kandinsky2":
-        from .kandinsky.pipeline import Kandinsky2Config, Kandinsky2Pipeline
-        pipe = Kandinsky2Pipeline(Kandinsky2Config.tiny() if tiny else Kandinsky2Config(), backend=backend,
-                                  device=device, dtype=dtype, model_dir=model_dir)
-        return pipe.predict
-    if name in ("zeroscopev2xl", "damo"):
-        from .video.pipeline import TextToVideoConfig, TextToVideoPipeline
-        cfg = TextToVideoConfig.tiny() if tiny else (TextToVideoConfig.zeroscope_xl() if name == "zeroscopev2xl"
-                                                      else TextToVideoConfig.damo())
-        pipe = TextToVideoPipeline(cfg, backend=backend, device=device, dtype=dtype, model_dir=model_dir, family=name)
-        return pipe.predict
-    if name == "robust_video_matting":
-        from .rvm.pipeline import RvmConfig, RvmPipeline
-        pipe = RvmPipeline(RvmConfig.tiny() if tiny else RvmConfig(), backend=backend, device=device, dtype=dtype,
-                           model_dir=model_dir)
-        return pipe.predict
-    raise ValueError(f"unknown model family {name!r}; choices: {FAMILIES}")
+    if dev.type != "cuda":
+        return _make_pipeline(name, device, model_dir, tiny, backend, dtype).predict
+    with torch.cuda.device(dev):
+        pipe = _make_pipeline(name, device, model_dir, tiny, backend, dtype)
+
+    def predict(inp: dict) -> bytes:
+        with torch.cuda.device(dev):
+            return pipe.predict(inp)
+
+    predict.pipeline = pipe           # the miner's cost model and the tests reach the pipeline through the callable
+    return predict

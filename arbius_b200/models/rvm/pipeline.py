@@ -148,7 +148,7 @@ class RvmPipeline:
             for r in st["rec"]:
                 r.zero_()
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with N.graph_capture(g):
                 self._frame(st, mode)
             st["graph"] = g
             for r in st["rec"]:

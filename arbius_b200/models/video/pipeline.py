@@ -174,7 +174,7 @@ class TextToVideoPipeline:
                 torch.cuda.synchronize()
                 graph = torch.cuda.CUDAGraph()
                 n0 = ops.native.launch_count()
-                with torch.cuda.graph(graph):
+                with ops.native.graph_capture(graph):
                     self._run_native(st, g)
                 st["launches"] = ops.native.launch_count() - n0
                 st["graph"] = graph

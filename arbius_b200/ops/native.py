@@ -7,9 +7,11 @@ library is a hard error: there is no silent PyTorch fallback for the native ops.
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import os
 import subprocess
+import threading
 from pathlib import Path
 from typing import Optional
 
@@ -65,6 +67,24 @@ class AttnArgs(C.Structure):
         ("causal", C.c_int),
         ("dtype", C.c_int),
     ]
+
+
+_CAPTURE_LOCK = threading.RLock()
+
+
+@contextlib.contextmanager
+def graph_capture(graph):
+    """``torch.cuda.graph`` for pipelines that may be driven from several threads (one predictor per GPU in one
+    process): captures are serialised process-wide (concurrent ``capture_begin`` calls fail with
+    cudaErrorIllegalState) and use thread-local capture mode so the other threads' replays and allocations neither
+    break the capture nor are broken by it. Replays stay concurrent."""
+    import torch
+    with _CAPTURE_LOCK:
+        # an explicit stream on the CURRENT device: torch.cuda.graph's default capture stream is created once per
+        # process on whichever device was current then, and entering it silently switches devices
+        stream = torch.cuda.Stream(device=torch.cuda.current_device())
+        with torch.cuda.graph(graph, stream=stream, capture_error_mode="thread_local"):
+            yield
 
 
 def lib_path() -> Path:

@@ -35,3 +35,28 @@ def test_fused_tp_gemms_are_bit_identical_to_single_gpu():
     sys.stdout.write(r.stdout[-3000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "bit-identical=False" not in r.stdout and "RESULT" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_one_process_drives_two_gpus_concurrently_with_identical_bytes():
+    """The miner's in-process GPU pool: one predictor per device on worker threads. Same task -> same bytes on every
+    GPU, also while both run (and capture their CUDA graphs) at the same time."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from arbius_b200.models.registry import build_predictor
+    inp = {"prompt": "arbius test cat", "negative_prompt": "", "width": 64, "height": 64, "num_inference_steps": 3,
+           "guidance_scale": 7.5, "scheduler": "DPMSolverMultistep", "seed": 1337}
+    preds = [build_predictor("anythingv3", device=f"cuda:{i}", tiny=True) for i in range(2)]
+    with ThreadPoolExecutor(max_workers=2) as pool:
+        first = list(pool.map(lambda p: p(inp), preds))             # graph capture happens here, concurrently
+        again = list(pool.map(lambda p: p(dict(inp)), preds))       # replay
+        other = list(pool.map(lambda pi: pi[0](dict(inp, seed=pi[1])), zip(preds, (1, 2))))
+    assert first[0] == first[1] == again[0] == again[1] and first[0][:4] == b"\x89PNG"
+    assert other[0] != first[0] and other[1] != other[0]
+    rvm = [build_predictor("robust_video_matting", device=f"cuda:{i}", tiny=True) for i in range(2)]
+    import numpy as np
+    clip = (np.arange(2 * 64 * 96 * 3, dtype=np.uint32) * 2654435761 >> 24).astype(np.uint8).reshape(2, 64, 96, 3)
+    with ThreadPoolExecutor(max_workers=2) as pool:
+        vids = list(pool.map(lambda p: p({"input_video": clip, "output_type": "alpha-mask"}), rvm))
+    assert vids[0] == vids[1] and vids[0][4:8] == b"ftyp"
