@@ -27,3 +27,13 @@ elif what == "gn":
         ops.groupnorm(x, g, g, 32, 1e-5, "silu")
 torch.cuda.synchronize()
 print("ok")
+if what == "tattn":
+    from arbius_b200.ops.temporal import temporal_attn
+    b, f, hw, heads, d = 2, 24, 9216, 5, 64
+    c = heads * d
+    qkv = torch.randn(b, f, hw, 3 * c, device="cuda", dtype=dt)
+    q, k, v = (qkv[..., i * c:(i + 1) * c] for i in range(3))
+    for _ in range(3):
+        temporal_attn(q, k, v, heads)
+    torch.cuda.synchronize()
+    print("ok")
