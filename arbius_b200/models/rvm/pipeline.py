@@ -88,6 +88,7 @@ class RvmPipeline:
             from .native import NativeRvm
             self.net = NativeRvm(net.state_dict(), cfg, dtype, device)
         self.use_graph = use_graph and backend == "native"
+        self.chunk_frames = 8            # frames per host<->device staging chunk (two chunks in flight each way)
         self._graphs: Dict[Tuple, dict] = {}
         self.h2d_bytes = self.d2h_bytes = 0
         self.last_launches = 0
@@ -127,16 +128,21 @@ class RvmPipeline:
         from ...ops import native as N
         T, H, W, _ = frames.shape
         st = self._state_for(T, H, W, mode)
-        host_in = torch.from_numpy(np.ascontiguousarray(frames)).pin_memory()
-        dev_in = host_in.to(self.device, non_blocking=True)
-        dev_out = torch.empty_like(dev_in)
-        self.h2d_bytes, self.d2h_bytes = host_in.numel(), host_in.numel()
+        frames = np.ascontiguousarray(frames)
+        self.h2d_bytes = self.d2h_bytes = frames.size
+        CH = self.chunk_frames
+        if "pin_in" not in st:          # two pinned + two device staging chunks each way, reused by every clip of this size
+            st["pin_in"] = [torch.empty((CH, H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+            st["pin_out"] = [torch.empty((CH, H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+            st["dev_in"] = [torch.empty((CH, H, W, 3), dtype=torch.uint8, device=self.device) for _ in range(2)]
+            st["dev_out"] = [torch.empty((CH, H, W, 3), dtype=torch.uint8, device=self.device) for _ in range(2)]
+            st["copy_stream"] = torch.cuda.Stream(device=self.device)
         for r in st["rec"]:
             r.zero_()
         lib = N.load()
         c0 = lib.ab_launch_count() if hasattr(lib, "ab_launch_count") else 0
         if self.use_graph and st["graph"] is None:
-            st["src"].copy_(dev_in[0:1])
+            st["src"].copy_(torch.from_numpy(frames[0:1]).to(self.device))
             s = torch.cuda.Stream(device=self.device)
             s.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(s):
@@ -153,18 +159,55 @@ class RvmPipeline:
             st["graph"] = g
             for r in st["rec"]:
                 r.zero_()
-        for t in range(T):
-            st["src"].copy_(dev_in[t:t + 1])
-            if st["graph"] is not None:
-                st["graph"].replay()
-            else:
-                self._frame(st, mode)
-            dev_out[t:t + 1].copy_(st["out"])
+        # Chunked pipeline: while the GPU mattes chunk k (compute stream), the copy stream brings chunk k+1 in and takes
+        # chunk k-1 out, and this thread fills / drains the pinned staging buffers. The recurrence only orders frames
+        # on the compute stream.
+        main, cs = torch.cuda.current_stream(self.device), st["copy_stream"]
+        result = np.empty_like(frames)
+        nchunk = (T + CH - 1) // CH
+        h2d_done = [torch.cuda.Event() for _ in range(2)]
+        comp_done = [torch.cuda.Event() for _ in range(2)]
+        d2h_done = [torch.cuda.Event() for _ in range(2)]
+
+        def stage_in(k: int) -> None:
+            b, lo, hi = k % 2, k * CH, min(T, (k + 1) * CH)
+            if k >= 2:
+                comp_done[b].synchronize()                  # dev_in[b] / pin_in[b] were last used by chunk k-2
+            np.copyto(st["pin_in"][b].numpy()[:hi - lo], frames[lo:hi])
+            with torch.cuda.stream(cs):
+                st["dev_in"][b][:hi - lo].copy_(st["pin_in"][b][:hi - lo], non_blocking=True)
+                h2d_done[b].record(cs)
+
+        def drain(k: int) -> None:
+            b, lo, hi = k % 2, k * CH, min(T, (k + 1) * CH)
+            d2h_done[b].synchronize()
+            np.copyto(result[lo:hi], st["pin_out"][b].numpy()[:hi - lo])
+
+        stage_in(0)
+        for k in range(nchunk):
+            b, lo, hi = k % 2, k * CH, min(T, (k + 1) * CH)
+            if k + 1 < nchunk:
+                stage_in(k + 1)
+            main.wait_event(h2d_done[b])
+            if k >= 2:
+                main.wait_event(d2h_done[b])                # dev_out[b] still being read out for chunk k-2
+            for t in range(hi - lo):
+                st["src"].copy_(st["dev_in"][b][t:t + 1])
+                if st["graph"] is not None:
+                    st["graph"].replay()
+                else:
+                    self._frame(st, mode)
+                st["dev_out"][b][t:t + 1].copy_(st["out"])
+            comp_done[b].record(main)
+            with torch.cuda.stream(cs):
+                cs.wait_event(comp_done[b])
+                st["pin_out"][b][:hi - lo].copy_(st["dev_out"][b][:hi - lo], non_blocking=True)
+                d2h_done[b].record(cs)
+            if k >= 1:
+                drain(k - 1)
+        drain(nchunk - 1)
         self.last_launches = st.get("per_frame", 0) * T
-        host_out = torch.empty(dev_out.shape, dtype=torch.uint8).pin_memory()
-        host_out.copy_(dev_out, non_blocking=True)
-        torch.cuda.synchronize(self.device)
-        return host_out.numpy().copy()
+        return result
 
     # ------------------------------------------------------------------------------------------------
     def predict(self, inp: dict) -> bytes:

@@ -37,9 +37,12 @@ struct ConvGenParams {
     int n, h, w_in, ho, wo, ks, stride, dilation, pad, cout, cout_pad, act;
 };
 
-template <typename T>
+// ALLW: the block's whole weight slice [ks*ks*ctot][16] (fp32) is staged once in dynamic shared memory — every RVM
+// layer fits (<= 98.5 KB) — so the tap/channel loops run without barriers; otherwise 32-channel slabs are staged per step.
+template <typename T, bool ALLW>
 __global__ void __launch_bounds__(CG_THREADS) conv_generic_kernel(const __grid_constant__ ConvGenParams p) {
-    __shared__ __align__(16) float ws[CG_CK][CG_CO];
+    __shared__ __align__(16) float ws[ALLW ? 1 : CG_CK][CG_CO];
+    extern __shared__ __align__(16) float wall[];
     const long long npix = static_cast<long long>(p.n) * p.ho * p.wo;
     const long long pix = static_cast<long long>(blockIdx.x) * CG_THREADS + threadIdx.x;
     const bool live = pix < npix;
@@ -55,6 +58,12 @@ __global__ void __launch_bounds__(CG_THREADS) conv_generic_kernel(const __grid_c
 #pragma unroll
     for (int j = 0; j < CG_CO; ++j) acc[j] = 0.f;
     const T* wt = reinterpret_cast<const T*>(p.w);
+    if constexpr (ALLW) {
+        const int total = p.ks * p.ks * p.ctot * CG_CO;
+        for (int i = threadIdx.x; i < total; i += CG_THREADS)
+            wall[i] = DT<T>::to_f(wt[static_cast<long long>(i / CG_CO) * p.cout_pad + co0 + (i % CG_CO)]);
+        __syncthreads();
+    }
 
     int coff = 0;
     for (int s = 0; s < p.nsrc; ++s) {
@@ -73,16 +82,22 @@ __global__ void __launch_bounds__(CG_THREADS) conv_generic_kernel(const __grid_c
             const long long pin = (static_cast<long long>(ni) * p.h + yi) * p.w_in + xi;
             for (int c0 = 0; c0 < cs; c0 += CG_CK) {
                 const int ck = min(CG_CK, cs - c0);
-                __syncthreads();
-                // stage weights [ck x 16] as fp32
-                for (int i = threadIdx.x; i < CG_CK * CG_CO; i += CG_THREADS) {
-                    const int ci = i / CG_CO, j = i % CG_CO;
-                    float v = 0.f;
-                    if (ci < ck)
-                        v = DT<T>::to_f(wt[(static_cast<long long>(tap) * p.ctot + coff + c0 + ci) * p.cout_pad + co0 + j]);
-                    ws[ci][j] = v;
+                const float* wbase;
+                if constexpr (ALLW) {
+                    wbase = wall + (static_cast<long long>(tap) * p.ctot + coff + c0) * CG_CO;
+                } else {
+                    __syncthreads();
+                    // stage weights [ck x 16] as fp32
+                    for (int i = threadIdx.x; i < CG_CK * CG_CO; i += CG_THREADS) {
+                        const int ci = i / CG_CO, j = i % CG_CO;
+                        float v = 0.f;
+                        if (ci < ck)
+                            v = DT<T>::to_f(wt[(static_cast<long long>(tap) * p.ctot + coff + c0 + ci) * p.cout_pad + co0 + j]);
+                        ws[ci][j] = v;
+                    }
+                    __syncthreads();
+                    wbase = &ws[0][0];
                 }
-                __syncthreads();
                 if (!inb) continue;
                 if (vec_s) {
                     for (int ci = 0; ci < ck; ci += 8) {
@@ -96,7 +111,7 @@ __global__ void __launch_bounds__(CG_THREADS) conv_generic_kernel(const __grid_c
                         }
 #pragma unroll
                         for (int u = 0; u < 8; ++u) {
-                            const float4* wr = reinterpret_cast<const float4*>(ws[ci + u]);
+                            const float4* wr = reinterpret_cast<const float4*>(wbase + (ci + u) * CG_CO);
 #pragma unroll
                             for (int q = 0; q < CG_CO / 4; ++q) {
                                 const float4 wv = wr[q];
@@ -112,7 +127,7 @@ __global__ void __launch_bounds__(CG_THREADS) conv_generic_kernel(const __grid_c
                         float f = DT<T>::to_f(src[pin * ld + c0 + ci]);
                         if (gate) f *= DT<T>::to_f(gate[pin * gld + c0 + ci]);
                         if (affine) f = f * p.in_scale[c0 + ci] + p.in_shift[c0 + ci];
-                        const float4* wr = reinterpret_cast<const float4*>(ws[ci]);
+                        const float4* wr = reinterpret_cast<const float4*>(wbase + ci * CG_CO);
 #pragma unroll
                         for (int q = 0; q < CG_CO / 4; ++q) {
                             const float4 wv = wr[q];
@@ -360,7 +375,14 @@ extern "C" int ab_conv_generic(const ab_conv_generic_args* a, void* stream_) {
     AB_REQUIRE(p.out_ld >= p.cout && p.ho > 0 && p.wo > 0, "bad output geometry");
     const long long npix = static_cast<long long>(p.n) * p.ho * p.wo;
     dim3 grid(static_cast<unsigned>((npix + ab::CG_THREADS - 1) / ab::CG_THREADS), p.cout_pad / ab::CG_CO);
-    AB_DISPATCH_M(a->dtype, (ab::conv_generic_kernel<T><<<grid, ab::CG_THREADS, 0, stream>>>(p)));
+    const size_t wbytes = static_cast<size_t>(p.ks) * p.ks * p.ctot * ab::CG_CO * sizeof(float);
+    if (wbytes <= 100 * 1024) {
+        if (ab_ensure_max_smem(reinterpret_cast<const void*>(ab::conv_generic_kernel<__half, true>), 100 * 1024)) return -1;
+        if (ab_ensure_max_smem(reinterpret_cast<const void*>(ab::conv_generic_kernel<__nv_bfloat16, true>), 100 * 1024)) return -1;
+        AB_DISPATCH_M(a->dtype, (ab::conv_generic_kernel<T, true><<<grid, ab::CG_THREADS, wbytes, stream>>>(p)));
+    } else {
+        AB_DISPATCH_M(a->dtype, (ab::conv_generic_kernel<T, false><<<grid, ab::CG_THREADS, 0, stream>>>(p)));
+    }
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(1);
     return 0;
