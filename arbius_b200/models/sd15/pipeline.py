@@ -78,8 +78,14 @@ def load_modules_from_dir(cfg: SD15Config, model_dir: str, device="cpu", dtype=t
 class SD15Pipeline:
     def __init__(self, cfg: SD15Config = SD15Config(), backend: str = "native", device: str = "cuda",
                  dtype: torch.dtype = torch.float16, seed: int = 0, model_dir: Optional[str] = None,
-                 use_graph: bool = True):
+                 use_graph: bool = True, cfg_parallel=None):
+        """``cfg_parallel``: a 2-rank ``PeerHeap``. The two classifier-free-guidance branches of every UNet step then run
+        on two GPUs (rank 0 the negative prompt, rank 1 the prompt), exchange their 64 KB noise predictions through peer
+        memory behind one device-side barrier per step, and both ranks apply the same combine and sampler update: one
+        task at roughly half the latency, with the bytes of the single-GPU run (same split-K choices, same order)."""
         self.cfg, self.backend, self.device, self.dtype = cfg, backend, torch.device(device), dtype
+        self.cfgp = cfg_parallel
+        assert cfg_parallel is None or (cfg_parallel.world == 2 and backend == "native"), "cfg_parallel needs a 2-rank heap"
         self.tokenizer = load_tokenizer(model_dir, cfg.clip.vocab_size)
         if model_dir:
             mods = load_modules_from_dir(cfg, model_dir, device, dtype)
@@ -157,14 +163,40 @@ class SD15Pipeline:
             s_in = sch.input_scale(i)
             for b in range(2):
                 ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=s_in)
-            e = self.unet.forward(st["xin"], temb[2 * i:2 * i + 2], kvs)
-            ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
+            if self.cfgp is None:
+                e = self.unet.forward(st["xin"], temb[2 * i:2 * i + 2], kvs)
+                ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
+            else:
+                self._cfg_parallel_step(st, i, temb, kvs, g)
             for dst, terms in sch.plan(i):
                 srcs = [(c, st["noise"][i] if s == "noise" else f[s]) for c, s in terms]
                 ops.lincomb(f[dst], srcs)
         ops.lincomb(None, [(1.0, f["x"])], dst_m=st["lat"], m_scale=1.0)
         img = self.vae.forward(st["lat"])
         st["u8"] = ops.finalize_u8(img)
+
+    def _cfg_parallel_step(self, st: dict, i: int, temb, kvs, g: float) -> None:
+        """This rank's guidance branch of step i, exchange through the peer heap, combine (same operand order as the
+        single-GPU ``cfg_step(e[1], e[0])``). Two exchange slots alternate by step parity, so one barrier per step is
+        enough: a rank overwrites slot p two steps later, after the barrier of the step in between."""
+        import sys
+        heap, r, par = self.cfgp, self.cfgp.rank, i & 1
+        gemm_mod = sys.modules["arbius_b200.ops.gemm"]
+        gemm_mod.BATCH_SCALE = 2                      # tile/split-K choices of the undivided batch of two
+        try:
+            e = self.unet.forward(st["xin"][r:r + 1], temb[2 * i + r:2 * i + r + 1], [kv[r:r + 1] for kv in kvs])
+        finally:
+            gemm_mod.BATCH_SCALE = 1
+        slot = st["ex"][par]
+        slot.copy_(e)
+        heap.barrier_replayable()
+        own = slot.data_ptr()
+        peer = heap.peer_ptr(1 - r, st["ex_off"] + par * slot.numel() * slot.element_size())
+        ptr_c, ptr_u = (own, peer) if r == 1 else (peer, own)
+        lib = ops.native.load()
+        ops.native.check(lib.ab_cfg_step(ptr_c, ptr_u, None, None, None, None, None, st["f32"]["eps"].data_ptr(),
+                                         slot.numel(), g, 0.0, 1.0, 0.0, 0.0, ops.native.dtype_code(slot.dtype),
+                                         ops.native.stream_ptr()), "ab_cfg_step")
 
     def _state(self, key, width, height, steps, g, sched_name) -> dict:
         st = self._graphs.get(key)
@@ -187,6 +219,8 @@ class SD15Pipeline:
                   lat=torch.zeros((1, h, w, 4), dtype=dt, device=dev),
                   out_host=torch.zeros((height, width, 3), dtype=torch.uint8).pin_memory(),
                   graph=None, launches=0)
+        if self.cfgp is not None:
+            st["ex"], st["ex_off"] = self.cfgp.alloc((2, 1, h, w, 4), dt)      # same offset on both ranks
         if self.use_graph:
             # warm-up run on a side stream (allocator + lazy kernel attribute setup), then capture
             s = torch.cuda.Stream()

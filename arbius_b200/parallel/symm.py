@@ -52,6 +52,8 @@ def _lib():
         lib.ab_ipc_close_handle.argtypes = [vp]
         lib.ab_peer_barrier.restype = C.c_int
         lib.ab_peer_barrier.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_uint, vp]
+        lib.ab_peer_barrier_auto.restype = C.c_int
+        lib.ab_peer_barrier_auto.argtypes = [C.POINTER(vp), C.c_int, C.c_int, vp]
         lib._peer_sigs = True
     return lib
 
@@ -116,6 +118,13 @@ class PeerHeap:
         arr = (C.c_void_p * self.world)(*self.ptrs)
         native.check(_lib().ab_peer_barrier(arr, self.rank, self.world, self._epoch, native.stream_ptr()),
                      "ab_peer_barrier")
+
+    def barrier_replayable(self) -> None:
+        """Device-side barrier whose epoch lives in device memory: safe to capture in a CUDA graph and replay."""
+        if self.world == 1:
+            return
+        arr = (C.c_void_p * self.world)(*self.ptrs)
+        native.check(_lib().ab_peer_barrier_auto(arr, self.rank, self.world, native.stream_ptr()), "ab_peer_barrier_auto")
 
     def close(self) -> None:
         lib = _lib()

@@ -56,7 +56,42 @@ __global__ void peer_barrier_kernel(PeerFlags f, int rank, int world, unsigned i
         } while (static_cast<int>(v - epoch) < 0);
     }
 }
+// Replayable form for CUDA graphs: the epoch is not a launch argument (a replayed graph would present the same value
+// again and fall straight through) but a counter in this rank's own flag page, advanced by the kernel itself. Every
+// rank executes the same sequence of these barriers, so the counters stay equal. It uses its own flag words
+// (u32 [32..40) of the page, counter at [64]) and must not be mixed with the host-epoch form on the same words.
+__global__ void peer_barrier_auto_kernel(PeerFlags f, int rank, int world) {
+    const int t = threadIdx.x;
+    unsigned int epoch = 0;
+    if (t == 0) {
+        unsigned int* cnt = f.flags[rank] + 64;
+        epoch = *cnt + 1;
+        *cnt = epoch;
+    }
+    epoch = __shfl_sync(0xffffffffu, epoch, 0);
+    if (t < world) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.flags[t] + 32 + rank), "r"(epoch) : "memory");
+        long long t0 = clock64();
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f.flags[rank] + 32 + t) : "memory");
+            if (clock64() - t0 > 20000000000LL) { printf("peer barrier (auto) timeout rank %d waiting for %d\n", rank, t); __trap(); }
+        } while (static_cast<int>(v - epoch) < 0);
+    }
+}
 }  // namespace ab
+
+extern "C" int ab_peer_barrier_auto(void* const* flag_ptrs, int rank, int world, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(flag_ptrs && world >= 1 && world <= 8 && rank >= 0 && rank < world, "bad arguments");
+    ab::PeerFlags f{};
+    for (int r = 0; r < world; ++r) f.flags[r] = reinterpret_cast<unsigned int*>(flag_ptrs[r]);
+    ab::peer_barrier_auto_kernel<<<1, 32, 0, stream>>>(f, rank, world);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
 
 extern "C" int ab_peer_barrier(void* const* flag_ptrs, int rank, int world, unsigned int epoch, void* stream_) {
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);

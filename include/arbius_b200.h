@@ -185,6 +185,8 @@ int ab_ipc_get_handle(void* ptr, unsigned char* handle64);
 int ab_ipc_open_handle(const unsigned char* handle64, void** ptr);
 int ab_ipc_close_handle(void* ptr);
 int ab_peer_barrier(void* const* flag_ptrs, int rank, int world, unsigned int epoch, void* stream);
+/* same barrier with the epoch kept in device memory (own flag words), so it can be captured in a CUDA graph and replayed */
+int ab_peer_barrier_auto(void* const* flag_ptrs, int rank, int world, void* stream);
 
 /* ---- K12/K15/G1/G3/S11: elementwise ------------------------------------------------------------- */
 /* counter-based N(0,1): out[i] = normal(philox4x32-10(seed, stream_id, offset + i)); i is the GLOBAL

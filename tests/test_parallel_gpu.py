@@ -60,3 +60,13 @@ def test_one_process_drives_two_gpus_concurrently_with_identical_bytes():
     with ThreadPoolExecutor(max_workers=2) as pool:
         vids = list(pool.map(lambda p: p({"input_video": clip, "output_type": "alpha-mask"}), rvm))
     assert vids[0] == vids[1] and vids[0][4:8] == b"ftyp"
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_guidance_parallel_sd15_matches_single_gpu_bytes():
+    """Two GPUs, one task: each runs one classifier-free-guidance branch; the image bytes equal the 1-GPU run."""
+    r = _torchrun("mp_cfg_parallel.py", 2, 29613, timeout=600)
+    sys.stdout.write(r.stdout[-3000:])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "bit-identical=False" not in r.stdout and "RESULT" in r.stdout
