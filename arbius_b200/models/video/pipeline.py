@@ -51,8 +51,14 @@ class TextToVideoConfig:
 
 class TextToVideoPipeline:
     def __init__(self, cfg: TextToVideoConfig, backend: str = "native", device: str = "cuda", dtype=torch.float16,
-                 seed: int = 0, model_dir: Optional[str] = None, family: str = "zeroscopev2xl", use_graph: bool = True):
+                 seed: int = 0, model_dir: Optional[str] = None, family: str = "zeroscopev2xl", use_graph: bool = True,
+                 cfg_parallel=None):
+        """``cfg_parallel``: a 2-rank ``PeerHeap`` — guidance parallelism as in ``SD15Pipeline``: each GPU runs one
+        classifier-free-guidance branch of every UNet3D step and the predictions are exchanged through peer memory.
+        The video kernels are large, so one task takes close to half the single-GPU time, with identical bytes."""
         self.cfg, self.backend, self.device, self.dtype, self.family = cfg, backend, torch.device(device), dtype, family
+        self.cfgp = cfg_parallel
+        assert cfg_parallel is None or (cfg_parallel.world == 2 and backend == "native"), "cfg_parallel needs a 2-rank heap"
         self.tokenizer = load_tokenizer(model_dir, cfg.clip.vocab_size)
         with torch.device(device):
             unet, clip, vae = UNet3DConditionModel(cfg.unet), CLIPTextModel(cfg.clip), AutoencoderKLDecoder(cfg.vae)
@@ -136,8 +142,11 @@ class TextToVideoPipeline:
         for i in range(len(sch.timesteps)):
             for b in range(2):
                 ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=sch.input_scale(i))
-            e = self.unet.forward(st["xin"], temb[2 * nf * i:2 * nf * (i + 1)], kvs)
-            ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
+            if self.cfgp is None:
+                e = self.unet.forward(st["xin"], temb[2 * nf * i:2 * nf * (i + 1)], kvs)
+                ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
+            else:
+                self._cfg_parallel_step(st, i, temb, kvs, g)
             for dst, terms in sch.plan(i):
                 ops.lincomb(f[dst], [(c, st["noise"][i] if s == "noise" else f[s]) for c, s in terms])
         ops.lincomb(None, [(1.0, f["x"])], dst_m=st["lat"], m_scale=1.0)
@@ -145,6 +154,28 @@ class TextToVideoPipeline:
         for i in range(0, nf, st["vae_chunk"]):
             chunks.append(ops.finalize_u8(self.vae.forward(st["lat"][0, i:i + st["vae_chunk"]])))
         st["u8"] = torch.cat(chunks, 0) if len(chunks) > 1 else chunks[0]
+
+    def _cfg_parallel_step(self, st: dict, i: int, temb, kvs, g: float) -> None:
+        """This rank's guidance branch of step i, exchanged through the peer heap (see SD15Pipeline._cfg_parallel_step)."""
+        import sys
+        heap, r, par, nf = self.cfgp, self.cfgp.rank, i & 1, st["nf"]
+        gemm_mod = sys.modules["arbius_b200.ops.gemm"]
+        gemm_mod.BATCH_SCALE = 2
+        try:
+            rows = temb[2 * nf * i + r * nf:2 * nf * i + (r + 1) * nf]
+            e = self.unet.forward(st["xin"][r:r + 1], rows, [kv[r:r + 1] for kv in kvs])
+        finally:
+            gemm_mod.BATCH_SCALE = 1
+        slot = st["ex"][par]
+        slot.copy_(e)
+        heap.barrier_replayable()
+        own = slot.data_ptr()
+        peer = heap.peer_ptr(1 - r, st["ex_off"] + par * slot.numel() * slot.element_size())
+        ptr_c, ptr_u = (own, peer) if r == 1 else (peer, own)
+        lib = ops.native.load()
+        ops.native.check(lib.ab_cfg_step(ptr_c, ptr_u, None, None, None, None, None, st["f32"]["eps"].data_ptr(),
+                                         slot.numel(), g, 0.0, 1.0, 0.0, 0.0, ops.native.dtype_code(slot.dtype),
+                                         ops.native.stream_ptr()), "ab_cfg_step")
 
     def _native(self, ids, nf, steps, width, height, g, sched, seed) -> np.ndarray:
         dev, dt = self.device, self.dtype
@@ -165,6 +196,8 @@ class TextToVideoPipeline:
                       xin=torch.zeros((2, nf, h, w, 4), dtype=dt, device=dev), lat=torch.zeros(shape, dtype=dt, device=dev),
                       out_host=torch.zeros((nf, height, width, 3), dtype=torch.uint8).pin_memory(),
                       vae_chunk=max(1, min(nf, (1 << 22) // max(1, height * width // 4))), graph=None, launches=0)
+            if self.cfgp is not None:
+                st["ex"], st["ex_off"] = self.cfgp.alloc((2,) + shape, dt)
             if self.use_graph:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())

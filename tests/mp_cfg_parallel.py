@@ -60,6 +60,43 @@ def main():
         t_ref = timeit(full_ref)
         if rank == 0:
             print(f"RESULT cfg_parallel world=2 latency_ms={t_par:.2f} single_gpu_latency_ms={t_ref:.2f}", flush=True)
+    # ---------------- text-to-video UNet3D ----------------
+    from arbius_b200.models.video.pipeline import TextToVideoConfig, TextToVideoPipeline
+    vref = TextToVideoPipeline(TextToVideoConfig.tiny(), backend="native", device=dev, dtype=torch.float16, family="video-tiny")
+    vpar = TextToVideoPipeline(TextToVideoConfig.tiny(), backend="native", device=dev, dtype=torch.float16, family="video-tiny",
+                               cfg_parallel=heap)
+    vkw = dict(prompt="a panda eating bamboo", negative_prompt="noisy", num_inference_steps=3)
+    a = vref.generate(seed=11, **vkw)
+    b1 = vpar.generate(seed=11, **vkw)
+    b2 = vpar.generate(seed=11, **vkw)
+    same = bool((a == b1).all() and (a == b2).all())
+    print(f"rank {rank} video-tiny bit-identical={same}", flush=True)
+    ok = ok and same
+    if os.environ.get("AB_CFGP_FULL", "1") == "1":
+        del full_ref, full_par
+        torch.cuda.empty_cache()
+        zcfg = TextToVideoConfig.zeroscope_xl()
+        zref = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16)
+        zpar = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16, cfg_parallel=heap)
+        zkw = dict(prompt="a panda eating bamboo on a rock", negative_prompt="noisy, washed out", num_inference_steps=4)
+        a = zref.generate(seed=3, **zkw)
+        b = zpar.generate(seed=3, **zkw)
+        same = bool((a == b).all())
+        print(f"rank {rank} ZeroScope XL 1024x576x24 (4 steps) bit-identical={same}", flush=True)
+        ok = ok and same
+
+        def vtime(p):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            p.generate(seed=21, **zkw)
+            torch.cuda.synchronize()
+            t = torch.tensor([(time.perf_counter() - t0) * 1e3], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.item()
+        t_par, t_ref = vtime(zpar), vtime(zref)
+        if rank == 0:
+            print(f"RESULT zeroscope cfg_parallel world=2 4-step latency_ms={t_par:.1f} single_gpu_latency_ms={t_ref:.1f}", flush=True)
     heap.close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
