@@ -91,6 +91,8 @@ def main() -> int:
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--denoise-steps", type=int, default=20)
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
+    ap.add_argument("--latency-mode", action="store_true",
+                    help="with >= 2 GPUs also time guidance-parallel pairs (one task over two GPUs) and add 'latency_mode'")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm()
@@ -227,6 +229,32 @@ def main() -> int:
                 "last_cid": cid},
         "gpu_launches": int(launches or eager_launches),
     }
+    if args.latency_mode and world >= 2 and world % 2 == 0 and args.impl == "native" and not args.model.startswith("kandinsky"):
+        # Optional second measurement: the same tasks with guidance parallelism (pairs of GPUs share one task: lower
+        # latency, byte-identical output). world/2 tasks are in flight at a time.
+        from arbius_b200.parallel.groups import subset_group
+        from arbius_b200.parallel.symm import PeerHeap
+        heap = PeerHeap(64 << 20, group=subset_group(2))
+        if video:
+            lpipe = TextToVideoPipeline(vcfg, backend="native", device=f"cuda:{local}", dtype=dt, family=args.model,
+                                        cfg_parallel=heap)
+        else:
+            lpipe = SD15Pipeline(cfg, backend="native", device=f"cuda:{local}", dtype=dt, seed=0, cfg_parallel=heap)
+        pair = rank // 2
+        for i in range(W):
+            lpipe.generate(seed=5000 + pair * 100 + i, **base)
+        barrier()
+        l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0.record()
+        for i in range(K):
+            lpipe.generate(seed=6000 + pair * 1000 + i, **base)
+        l1.record()
+        barrier()
+        lat_ms_pair = reduce_max(l0.elapsed_time(l1)) / K
+        out["latency_mode"] = {"parallelism": f"guidance-parallel pairs x task-dp{world // 2}", "ms_per_task": round(lat_ms_pair, 3),
+                               "tasks_per_hour": round((world // 2) / (lat_ms_pair / 1e3) * 3600.0, 2),
+                               "bytes": "identical to the single-GPU pipeline (tests/mp_cfg_parallel.py)"}
+        heap.close()
     if rank == 0:
         print(json.dumps(out))
     if world > 1:
