@@ -50,3 +50,59 @@ def build_predictor(name: str, device: str = "cuda:0", model_dir: Optional[str] 
 
     predict.pipeline = pipe           # the miner's cost model and the tests reach the pipeline through the callable
     return predict
+
+
+PAIR_FAMILIES = ("anythingv3", "zeroscopev2xl", "damo")
+
+
+def build_pair_predictor(name: str, devices=(0, 1), model_dir: Optional[str] = None, tiny: bool = False,
+                         dtype=None) -> Callable[[dict], bytes]:
+    """One task over TWO GPUs of this process (a 2-GPU subset of the miner's pool): guidance parallelism — each device
+    runs one classifier-free-guidance branch per UNet step, predictions cross through peer memory, both produce the
+    same bytes as the single-GPU pipeline; the first device's output is returned. Lower latency, not more throughput:
+    the scheduler only picks it when GPUs would otherwise idle."""
+    import threading
+
+    import torch
+
+    from ..parallel.symm import PeerHeap
+    if name not in PAIR_FAMILIES:
+        raise ValueError(f"{name!r} has no 2-GPU form; choices: {PAIR_FAMILIES}")
+    assert len(devices) == 2
+    dtype = dtype or torch.float16
+    heaps = PeerHeap.local_group(64 << 20, devices)
+    pipes = []
+    for d, heap in zip(devices, heaps):
+        with torch.cuda.device(d):
+            if name == "anythingv3":
+                from .sd15.pipeline import SD15Config, SD15Pipeline
+                pipes.append(SD15Pipeline(SD15Config.tiny() if tiny else SD15Config(), backend="native", device=f"cuda:{d}",
+                                          dtype=dtype, model_dir=model_dir, cfg_parallel=heap))
+            else:
+                from .video.pipeline import TextToVideoConfig, TextToVideoPipeline
+                cfg = TextToVideoConfig.tiny() if tiny else (TextToVideoConfig.zeroscope_xl() if name == "zeroscopev2xl"
+                                                              else TextToVideoConfig.damo())
+                pipes.append(TextToVideoPipeline(cfg, backend="native", device=f"cuda:{d}", dtype=dtype,
+                                                 model_dir=model_dir, family=name, cfg_parallel=heap))
+
+    def predict(inp: dict) -> bytes:
+        out = [None, None]
+
+        def run(i: int) -> None:
+            try:
+                with torch.cuda.device(devices[i]):
+                    out[i] = pipes[i].predict(dict(inp))
+            except BaseException as e:                      # noqa: BLE001 - re-raised on the calling thread
+                out[i] = e
+        threads = [threading.Thread(target=run, args=(i,)) for i in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        for o in out:
+            if isinstance(o, BaseException):
+                raise o
+        return out[0]
+
+    predict.pipelines = pipes
+    return predict

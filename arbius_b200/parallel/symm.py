@@ -126,8 +126,44 @@ class PeerHeap:
         arr = (C.c_void_p * self.world)(*self.ptrs)
         native.check(_lib().ab_peer_barrier_auto(arr, self.rank, self.world, native.stream_ptr()), "ab_peer_barrier_auto")
 
+    @classmethod
+    def local_group(cls, nbytes: int, devices: Sequence[int]) -> List["PeerHeap"]:
+        """One heap per device of THIS process (the miner's in-process GPU pool): no IPC handles, the peers'
+        allocations are addressed directly once peer access is enabled. Returns the heaps in ``devices`` order; each
+        must be used from a thread whose current device is its own."""
+        lib = _lib()
+        heaps = []
+        for r, d in enumerate(devices):
+            h = cls.__new__(cls)
+            h.group, h.rank, h.world, h._local, h.device = None, r, len(devices), True, int(d)
+            h.nbytes = int(nbytes) + _FLAG_BYTES
+            with torch.cuda.device(d):
+                base = C.c_void_p()
+                native.check(lib.ab_heap_alloc(C.byref(base), h.nbytes), "ab_heap_alloc")
+                h.base = base.value
+                h._bytes = torch.as_tensor(_CudaArray(h.base, h.nbytes), device=f"cuda:{d}")
+            h._opened, h._epoch, h._cursor = [], 0, _FLAG_BYTES
+            heaps.append(h)
+        for a in devices:                      # torch enables peer access lazily on the first cross-device copy
+            for b in devices:
+                if a != b:
+                    assert torch.cuda.can_device_access_peer(a, b), f"no peer access {a} -> {b}"
+                    torch.empty(1, device=f"cuda:{a}").copy_(torch.empty(1, device=f"cuda:{b}"))
+        for h in heaps:
+            h.ptrs = [x.base for x in heaps]
+        torch.cuda.synchronize()
+        return heaps
+
     def close(self) -> None:
         lib = _lib()
+        if getattr(self, "_local", False):
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize()
+                if self.base:
+                    self._bytes = None
+                    lib.ab_heap_free(self.base)
+                    self.base = 0
+            return
         torch.cuda.synchronize()
         if self.world > 1:
             dist.barrier(group=self.group)

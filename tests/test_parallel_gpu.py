@@ -70,3 +70,21 @@ def test_guidance_parallel_sd15_matches_single_gpu_bytes():
     sys.stdout.write(r.stdout[-3000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "bit-identical=False" not in r.stdout and "RESULT" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_pair_predictor_in_one_process_matches_single_gpu_bytes():
+    """A 2-GPU subset of the in-process pool: guidance-parallel predictor (threads + direct peer access, no IPC)."""
+    from arbius_b200.models.registry import build_pair_predictor, build_predictor
+    inp = {"prompt": "arbius test cat", "negative_prompt": "blurry", "width": 64, "height": 64, "num_inference_steps": 4,
+           "guidance_scale": 7.5, "scheduler": "DPMSolverMultistep", "seed": 99}
+    single = build_predictor("anythingv3", device="cuda:0", tiny=True)
+    pair = build_pair_predictor("anythingv3", devices=(0, 1), tiny=True)
+    ref = single(inp)
+    assert pair(inp) == ref and pair(dict(inp)) == ref              # capture, then replay
+    assert pair(dict(inp, seed=100)) == single(dict(inp, seed=100))
+    vin = {"prompt": "a panda", "negative_prompt": "noisy", "num_inference_steps": 3, "seed": 5}
+    vsingle = build_predictor("zeroscopev2xl", device="cuda:1", tiny=True)
+    vpair = build_pair_predictor("zeroscopev2xl", devices=(0, 1), tiny=True)
+    assert vpair(vin) == vsingle(vin)
