@@ -45,7 +45,9 @@ def encode_cog_output(data: bytes, mime: str) -> dict:
 class MLBackend:
     name = "base"
 
-    def getfiles(self, model: ModelEntry, taskid: str, inp: dict) -> Dict[str, bytes]:
+    def getfiles(self, model: ModelEntry, taskid: str, inp: dict, endpoint: Optional[int] = None,
+                 gpus: Optional[tuple] = None) -> Dict[str, bytes]:
+        """``gpus`` is the subset the scheduler gave this solve (None: the backend picks an endpoint itself)."""
         raise NotImplementedError
 
     def endpoints(self, model: ModelEntry) -> int:
@@ -81,8 +83,10 @@ class CogBackend(MLBackend):
     def endpoints(self, model: ModelEntry) -> int:
         return len(self.urls(model))
 
-    def getfiles(self, model, taskid, inp, endpoint: Optional[int] = None):
+    def getfiles(self, model, taskid, inp, endpoint: Optional[int] = None, gpus=None):
         urls = self.urls(model)
+        if endpoint is None and gpus:
+            endpoint = gpus[0]                         # one worker per GPU: the scheduler's subset names it
         if endpoint is None:
             with self._lock:
                 endpoint = self._rr.get(model.id, 0)
@@ -108,7 +112,7 @@ class ReplicateBackend(MLBackend):
             raise MLError(f"cannot derive replicate model from {docker}")
         return f"{m.group(1)}:{m.group(2)}"
 
-    def getfiles(self, model, taskid, inp):
+    def getfiles(self, model, taskid, inp, endpoint=None, gpus=None):
         if self._run is None:
             raise MLError("replicate strategy needs network access and an api_token; use 'cog' or 'native'")
         out = self._run(self.model_ref(model.template), {"input": inp})
@@ -121,8 +125,13 @@ class NativeBackend(MLBackend):
     (one per GPU subset); each is guarded by its own lock so one GPU never runs two tasks at once."""
     name = "native"
 
-    def __init__(self, predictors: Dict[str, List[Callable[[dict], Dict[str, bytes]]]]):
+    def __init__(self, predictors: Dict[str, List[Callable[[dict], Dict[str, bytes]]]],
+                 subset_predictors: Optional[Dict[str, Dict[tuple, Callable]]] = None):
+        """``subset_predictors[modelid][(g0, g1)]``: a predictor that spreads ONE task over that GPU subset (the
+        guidance-parallel pair predictors of models/registry.py); used when the scheduler hands a solve that subset."""
         self.predictors = {k.lower(): list(v) for k, v in predictors.items()}
+        self.subset_predictors = {k.lower(): {tuple(s): f for s, f in v.items()}
+                                  for k, v in (subset_predictors or {}).items()}
         self._locks = {k: [threading.Lock() for _ in v] for k, v in self.predictors.items()}
         self._rr: Dict[str, int] = {}
         self._lock = threading.Lock()
@@ -130,28 +139,49 @@ class NativeBackend(MLBackend):
     def endpoints(self, model):
         return len(self.predictors.get(model.id.lower(), []))
 
-    def getfiles(self, model, taskid, inp, endpoint: Optional[int] = None):
-        preds = self.predictors.get(model.id.lower())
+    def subset_sizes(self, model) -> List[int]:
+        """GPU counts one task of this model can be spread over (1 always; 2 when pair predictors were built)."""
+        return sorted({1} | {len(s) for s in self.subset_predictors.get(model.id.lower(), {})})
+
+    def getfiles(self, model, taskid, inp, endpoint: Optional[int] = None, gpus=None):
+        mid = model.id.lower()
+        preds = self.predictors.get(mid)
         if not preds:
             raise MLError(f"no native predictor for model {model.id}")
+        if gpus and len(gpus) > 1:
+            sub = self.subset_predictors.get(mid, {}).get(tuple(gpus))
+            if sub is not None:
+                locks = [self._locks[mid][g % len(preds)] for g in gpus]
+                for lk in locks:                      # ascending GPU order everywhere: no lock cycles
+                    lk.acquire()
+                try:
+                    out = sub(inp)
+                finally:
+                    for lk in reversed(locks):
+                        lk.release()
+                if isinstance(out, (bytes, bytearray)):
+                    out = {output_filename(model.template): bytes(out)}
+                return out
+        if endpoint is None and gpus:
+            endpoint = gpus[0]
         if endpoint is None:
             with self._lock:
                 endpoint = self._rr.get(model.id, 0)
                 self._rr[model.id] = (endpoint + 1) % len(preds)
         i = endpoint % len(preds)
-        with self._locks[model.id.lower()][i]:
+        with self._locks[mid][i]:
             out = preds[i](inp)
         if isinstance(out, (bytes, bytearray)):
             out = {output_filename(model.template): bytes(out)}
         return out
 
 
-def make_backend(c, native_predictors: Optional[dict] = None) -> MLBackend:
+def make_backend(c, native_predictors: Optional[dict] = None, subset_predictors: Optional[dict] = None) -> MLBackend:
     s = c.ml.strategy
     if s == "cog":
         return CogBackend(c.ml.cog)
     if s == "replicate":
         return ReplicateBackend((c.ml.replicate or {}).get("api_token"))
     if s == "native":
-        return NativeBackend(native_predictors or {})
+        return NativeBackend(native_predictors or {}, subset_predictors)
     raise MLError(f"unknown ml strategy {s!r}")

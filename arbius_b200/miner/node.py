@@ -211,7 +211,7 @@ class MinerNode:
         """``default__getcid`` (models.ts:34-54): files -> wrapped-directory CIDv0 -> 0x hex."""
         if self.c.evilmode:
             return EVIL_CID
-        files = self._retry(lambda: self.ml.getfiles(model, taskid, inp))
+        files = self._retry(lambda: self.ml.getfiles(model, taskid, inp, gpus=tuple(gpus) if gpus else None))
         if not files:
             log.error("task (%s) getfiles failed", taskid)
             return None
@@ -355,7 +355,9 @@ class MinerNode:
             if job.method == "solve":
                 d = job.decoded()
                 task = self.db.get_task(d["taskid"]) or {}
-                family = task.get("modelid", "unknown")
+                mid = str(task.get("modelid", "unknown")).lower()
+                # the cost model is keyed by model family (template name); unknown ids keep their id as the key
+                family = next((m.name for m in self.models if m.id.lower() == mid and m.name), mid)
                 fut = self.pool.submit(family, lambda gpus, j=job: self._run_job(j, gpus), priority=job.priority,
                                        age_key=float(task.get("blocktime") or 0))
                 with self._lock:

@@ -35,6 +35,18 @@ class CostModel:
     efficiency: float = 0.5            # assumed parallel efficiency per doubling when unmeasured:
     #                                    0.5 = "no speed-up" — tasks are only widened on measured evidence
 
+    # ms per task measured on B200 at the template defaults (profiles/multigpu_n8_v1.md); the P=2 rows are
+    # the guidance-parallel pair predictors and only count where such a predictor was actually built
+    MEASURED_B200 = {"anythingv3": {1: 127.0, 2: 110.0}, "zeroscopev2xl": {1: 15000.0, 2: 7800.0},
+                     "kandinsky2": {1: 972.0}}
+
+    @classmethod
+    def measured_b200(cls, pair_families: Sequence[str] = ()) -> "CostModel":
+        table = {}
+        for fam, row in cls.MEASURED_B200.items():
+            table[fam] = {p: ms for p, ms in row.items() if p == 1 or fam in pair_families}
+        return cls(table=table)
+
     def ms(self, family: str, p: int) -> float:
         t = self.table.get(family)
         if not t:

@@ -87,10 +87,27 @@ def start(config_path: str, run: bool = True) -> MinerNode:
             ent = c.ml.native.get("models", {}).get(m.id, {})
             predictors[m.id] = [build_predictor(m.name, device=f"cuda:{g}", model_dir=ent.get("weights"),
                                                 tiny=bool(ent.get("tiny"))) for g in range(gpus)]
-    ml = make_backend(c, predictors)
+    # ``ml.native.pairs: true`` also builds one guidance-parallel predictor per aligned GPU pair for the families that
+    # have one; the cost model then knows their measured 2-GPU latency and the latency policy may use them.
+    subset_predictors, pair_families, cost = {}, [], None
+    if c.ml.strategy == "native":
+        from ..models.registry import PAIR_FAMILIES, build_pair_predictor
+        from .scheduler import CostModel
+        gpus = int(c.ml.native.get("gpus", 1))
+        if c.ml.native.get("pairs") and gpus >= 2:
+            for m in models:
+                if m.name in PAIR_FAMILIES:
+                    ent = c.ml.native.get("models", {}).get(m.id, {})
+                    subset_predictors[m.id] = {(g, g + 1): build_pair_predictor(m.name, devices=(g, g + 1),
+                                                                                model_dir=ent.get("weights"),
+                                                                                tiny=bool(ent.get("tiny")))
+                                               for g in range(0, gpus - 1, 2)}
+                    pair_families.append(m.name)
+        cost = CostModel.measured_b200(pair_families)
+    ml = make_backend(c, predictors, subset_predictors)
     n_gpus = c.scheduler.gpus or max([ml.endpoints(m) for m in models] + [1])
     n_gpus = max(p for p in (1, 2, 4, 8) if p <= n_gpus)
-    node = MinerNode(c, chain, ml, models, db=db, n_gpus=n_gpus, pin=c.ipfs.strategy != "local")
+    node = MinerNode(c, chain, ml, models, db=db, n_gpus=n_gpus, cost=cost, pin=c.ipfs.strategy != "local")
     initialize_rpc(db, c.rpc.host, c.rpc.port, node)
     if run:
         node.run_forever()

@@ -200,6 +200,44 @@ def test_scheduler_simulation_beats_serial_reference():
     assert lat["p50_latency_s"] < 0.5 * thr1["p50_latency_s"]
 
 
+def test_scheduler_subset_reaches_the_backend_and_pairs_run_on_both_gpus():
+    """A lone task under the latency policy gets an aligned GPU pair when a pair predictor with a measured gain exists;
+    the backend then runs THAT subset's predictor while holding both GPUs; with a full queue tasks go one per GPU."""
+    eng = deploy_local(engine_balance=599990 * UNIT, funded={MINER: 50 * UNIT, USER: 50 * UNIT})
+    mid = eng.register_model(USER, USER, 0, template_bytes("anythingv3"))
+    model = ModelEntry(id=mid, template=load_template("anythingv3"), filters=[MiningFilter()], name="anythingv3")
+    single_calls, pair_calls = [], []
+    ml = None
+
+    def single(g):
+        def f(inp):
+            single_calls.append(g)
+            return FIXED_PNG + str(inp["seed"]).encode()
+        return f
+
+    def pair(inp):
+        pair_calls.append([lk.locked() for lk in ml._locks[mid.lower()]])
+        return FIXED_PNG + str(inp["seed"]).encode()
+    ml = NativeBackend({mid: [single(0), single(1)]}, {mid: {(0, 1): pair}})
+    assert ml.subset_sizes(model) == [1, 2]
+    cfg = parse_mining_config({"db_path": ":memory:", "ml": {"strategy": "native"}, "ipfs": {"strategy": "local"},
+                               "automine": {"enabled": False}, "scheduler": {"policy": "latency"}})
+    node = MinerNode(cfg, SimChainClient(eng, MINER), ml, [model], db=MinerDB(":memory:"), n_gpus=2,
+                     cost=CostModel.measured_b200(["anythingv3"]), sleep=lambda s: None)
+    node.bootup()
+    node.run_until_idle()
+    tid = _submit(eng, mid, {"prompt": "alone", "negative_prompt": ""})
+    node.run_until_idle()
+    assert pair_calls == [[True, True]] and single_calls == []
+    assert node.solved[-1]["gpus"] == (0, 1) and tid in eng.solutions
+    # explicit single-GPU subsets go to that GPU's predictor
+    ml.getfiles(model, "0x0", {"seed": 1}, gpus=(1,))
+    assert single_calls == [1]
+    # without a measured pair row nothing is widened
+    assert CostModel.measured_b200([]).best_latency_p("anythingv3", 2) == 1
+    assert CostModel.measured_b200(["zeroscopev2xl"]).best_latency_p("zeroscopev2xl", 8) == 2
+
+
 def test_gpu_pool_runs_and_learns_costs():
     pool = GpuPool(2, CostModel(), policy="throughput")
     futs = [pool.submit("sd", lambda gpus, i=i: (time.sleep(0.01), i, gpus)[1:], priority=1) for i in range(6)]
