@@ -120,19 +120,54 @@ class ReplicateBackend(MLBackend):
         return {output_filename(model.template): bytes(data)}
 
 
+class _SlotLock:
+    """A GPU's admission lock: up to ``slots`` single-GPU solves at once, or one exclusive holder (a subset solve)."""
+
+    def __init__(self, slots: int = 1):
+        self.slots, self._used = slots, 0
+        self._cv = threading.Condition()
+
+    def acquire_all(self) -> None:
+        with self._cv:
+            self._cv.wait_for(lambda: self._used == 0)
+            self._used = self.slots
+
+    def release_all(self) -> None:
+        with self._cv:
+            self._used = 0
+            self._cv.notify_all()
+
+    def locked(self) -> bool:
+        return self._used > 0
+
+    def __enter__(self):
+        with self._cv:
+            self._cv.wait_for(lambda: self._used < self.slots)
+            self._used += 1
+        return self
+
+    def __exit__(self, *exc):
+        with self._cv:
+            self._used -= 1
+            self._cv.notify_all()
+
+
 class NativeBackend(MLBackend):
     """In-process predictors. ``predictors[modelid]`` is a list of callables ``inp -> {filename: bytes}``
     (one per GPU subset); each is guarded by its own lock so one GPU never runs two tasks at once."""
     name = "native"
 
     def __init__(self, predictors: Dict[str, List[Callable[[dict], Dict[str, bytes]]]],
-                 subset_predictors: Optional[Dict[str, Dict[tuple, Callable]]] = None):
+                 subset_predictors: Optional[Dict[str, Dict[tuple, Callable]]] = None, slots: int = 1):
         """``subset_predictors[modelid][(g0, g1)]``: a predictor that spreads ONE task over that GPU subset (the
-        guidance-parallel pair predictors of models/registry.py); used when the scheduler hands a solve that subset."""
+        guidance-parallel pair predictors of models/registry.py); used when the scheduler hands a solve that subset.
+        ``slots`` > 1: that many solves may be inside one GPU's predictor at once (a ``BatchingPredictor`` merges them
+        into one graph replay); a subset solve still takes its GPUs exclusively."""
+        self.slots = max(1, int(slots))
         self.predictors = {k.lower(): list(v) for k, v in predictors.items()}
         self.subset_predictors = {k.lower(): {tuple(s): f for s, f in v.items()}
                                   for k, v in (subset_predictors or {}).items()}
-        self._locks = {k: [threading.Lock() for _ in v] for k, v in self.predictors.items()}
+        self._locks = {k: [_SlotLock(self.slots) for _ in v] for k, v in self.predictors.items()}
         self._rr: Dict[str, int] = {}
         self._lock = threading.Lock()
 
@@ -153,12 +188,12 @@ class NativeBackend(MLBackend):
             if sub is not None:
                 locks = [self._locks[mid][g % len(preds)] for g in gpus]
                 for lk in locks:                      # ascending GPU order everywhere: no lock cycles
-                    lk.acquire()
+                    lk.acquire_all()
                 try:
                     out = sub(inp)
                 finally:
                     for lk in reversed(locks):
-                        lk.release()
+                        lk.release_all()
                 if isinstance(out, (bytes, bytearray)):
                     out = {output_filename(model.template): bytes(out)}
                 return out
@@ -176,12 +211,13 @@ class NativeBackend(MLBackend):
         return out
 
 
-def make_backend(c, native_predictors: Optional[dict] = None, subset_predictors: Optional[dict] = None) -> MLBackend:
+def make_backend(c, native_predictors: Optional[dict] = None, subset_predictors: Optional[dict] = None,
+                 slots: int = 1) -> MLBackend:
     s = c.ml.strategy
     if s == "cog":
         return CogBackend(c.ml.cog)
     if s == "replicate":
         return ReplicateBackend((c.ml.replicate or {}).get("api_token"))
     if s == "native":
-        return NativeBackend(native_predictors or {}, subset_predictors)
+        return NativeBackend(native_predictors or {}, subset_predictors, slots)
     raise MLError(f"unknown ml strategy {s!r}")

@@ -45,13 +45,13 @@ class MinerNode:
     def __init__(self, config: MiningConfig, chain: ChainClient, ml: MLBackend, models: Sequence[ModelEntry],
                  db: Optional[MinerDB] = None, n_gpus: int = 1, cost: Optional[CostModel] = None,
                  sleep: Callable[[float], None] = time.sleep, retry_sleep: Optional[Callable[[float], None]] = None,
-                 pin: bool = False):
+                 pin: bool = False, slots: int = 1):
         self.c = config
         self.chain = chain
         self.ml = ml
         self.models = list(models)
         self.db = db or MinerDB(config.db_path)
-        self.pool = GpuPool(n_gpus, cost, policy=config.scheduler.policy)
+        self.pool = GpuPool(n_gpus, cost, policy=config.scheduler.policy, slots=slots)   # slots: solves per GPU at once
         self._sleep = sleep
         self._retry_sleep = retry_sleep or sleep
         self.pin = pin

@@ -86,22 +86,35 @@ class _Queued:
 
 
 class SubsetPlanner:
-    """Tracks which GPUs are free and hands out aligned power-of-two subsets."""
+    """Tracks which GPUs are free and hands out aligned power-of-two subsets. ``slots`` > 1 lets that many single-GPU
+    tasks share a GPU (the predictor batches them into one graph replay); wider subsets need wholly idle GPUs."""
 
-    def __init__(self, n_gpus: int):
+    def __init__(self, n_gpus: int, slots: int = 1):
         if n_gpus not in SUBSET_SIZES:
             raise ValueError("n_gpus must be 1, 2, 4 or 8")
         self.n = n_gpus
-        self.busy = [False] * n_gpus
+        self.slots = max(1, int(slots))
+        self.load = [0] * n_gpus
+
+    @property
+    def busy(self) -> List[bool]:
+        return [c > 0 for c in self.load]
 
     def free_count(self) -> int:
-        return self.busy.count(False)
+        """Free task slots (= idle GPUs when slots == 1)."""
+        return sum(self.slots - c for c in self.load)
 
     def acquire(self, p: int) -> Optional[Tuple[int, ...]]:
+        if p == 1:
+            g = min(range(self.n), key=lambda i: (self.load[i], i))      # spread first, then fill second slots
+            if self.load[g] >= self.slots:
+                return None
+            self.load[g] += 1
+            return (g,)
         for start in range(0, self.n, p):
-            if not any(self.busy[start:start + p]):
+            if not any(self.load[start:start + p]):
                 for i in range(start, start + p):
-                    self.busy[i] = True
+                    self.load[i] = self.slots
                 return tuple(range(start, start + p))
         return None
 
@@ -109,14 +122,19 @@ class SubsetPlanner:
         for p in reversed(SUBSET_SIZES):
             if p > self.n:
                 continue
+            if p == 1:
+                return 1 if min(self.load) < self.slots else 0
             for start in range(0, self.n, p):
-                if not any(self.busy[start:start + p]):
+                if not any(self.load[start:start + p]):
                     return p
         return 0
 
     def release(self, gpus: Sequence[int]) -> None:
+        if len(gpus) == 1:
+            self.load[gpus[0]] -= 1
+            return
         for i in gpus:
-            self.busy[i] = False
+            self.load[i] = 0
 
     def choose_p(self, family: str, waiting: int, cost: CostModel, policy: str) -> int:
         """How many GPUs the next task gets, given ``waiting`` queued tasks (including it)."""
@@ -126,7 +144,7 @@ class SubsetPlanner:
         if policy == "throughput" and waiting >= self.free_count():
             return min(cost.best_throughput_p(family, avail), avail)
         # fewer tasks than free GPUs (or latency policy): spread free GPUs over the waiting tasks
-        share = max(1, self.free_count() // max(waiting, 1))
+        share = max(1, self.load.count(0) // max(waiting, 1))
         cap = 1
         for p in SUBSET_SIZES:
             if p <= share and p <= avail:
@@ -139,8 +157,8 @@ class GpuPool:
     predictor lives (thread here; a worker process per GPU in production)."""
 
     def __init__(self, n_gpus: int, cost: Optional[CostModel] = None, policy: str = "throughput",
-                 clock: Callable[[], float] = time.monotonic):
-        self.planner = SubsetPlanner(n_gpus)
+                 clock: Callable[[], float] = time.monotonic, slots: int = 1):
+        self.planner = SubsetPlanner(n_gpus, slots)
         self.cost = cost or CostModel()
         self.policy = policy
         self._clock = clock

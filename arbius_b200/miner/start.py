@@ -80,13 +80,16 @@ def start(config_path: str, run: bool = True) -> MinerNode:
                                    STATIC_CHAIN_CONFIG["engineAddress"], STATIC_CHAIN_CONFIG["baseTokenAddress"])
     models = enabled_models(c, registered)
     predictors = {}
+    # ``ml.native.task_batch: n`` lets n solves share a GPU: the SD-1.5 predictor merges them into one graph replay
+    # (more tasks/hour, same bytes per task); the pool and the backend then admit n solves per GPU.
+    slots = int(c.ml.native.get("task_batch", 1)) if (c.ml.strategy == "native" and c.ml.native) else 1
     if c.ml.strategy == "native":
         from ..models.registry import build_predictor
         gpus = int(c.ml.native.get("gpus", 1))
         for m in models:
             ent = c.ml.native.get("models", {}).get(m.id, {})
             predictors[m.id] = [build_predictor(m.name, device=f"cuda:{g}", model_dir=ent.get("weights"),
-                                                tiny=bool(ent.get("tiny"))) for g in range(gpus)]
+                                                tiny=bool(ent.get("tiny")), task_batch=slots) for g in range(gpus)]
     # ``ml.native.pairs: true`` also builds one guidance-parallel predictor per aligned GPU pair for the families that
     # have one; the cost model then knows their measured 2-GPU latency and the latency policy may use them.
     subset_predictors, pair_families, cost = {}, [], None
@@ -104,10 +107,11 @@ def start(config_path: str, run: bool = True) -> MinerNode:
                                                for g in range(0, gpus - 1, 2)}
                     pair_families.append(m.name)
         cost = CostModel.measured_b200(pair_families)
-    ml = make_backend(c, predictors, subset_predictors)
+    ml = make_backend(c, predictors, subset_predictors, slots)
     n_gpus = c.scheduler.gpus or max([ml.endpoints(m) for m in models] + [1])
     n_gpus = max(p for p in (1, 2, 4, 8) if p <= n_gpus)
-    node = MinerNode(c, chain, ml, models, db=db, n_gpus=n_gpus, cost=cost, pin=c.ipfs.strategy != "local")
+    node = MinerNode(c, chain, ml, models, db=db, n_gpus=n_gpus, cost=cost, pin=c.ipfs.strategy != "local",
+                     slots=slots)
     initialize_rpc(db, c.rpc.host, c.rpc.port, node)
     if run:
         node.run_forever()

@@ -34,7 +34,9 @@ def _make_pipeline(name: str, device: str, model_dir: Optional[str], tiny: bool,
 
 
 def build_predictor(name: str, device: str = "cuda:0", model_dir: Optional[str] = None, tiny: bool = False,
-                    backend: Optional[str] = None, dtype=None) -> Callable[[dict], bytes]:
+                    backend: Optional[str] = None, dtype=None, task_batch: int = 1) -> Callable[[dict], bytes]:
+    """``task_batch`` > 1 (families in ``BATCH_FAMILIES``, native backend) returns a ``BatchingPredictor``: a callable
+    that may be entered by ``task_batch`` threads at once and runs their tasks in one graph replay."""
     import torch
     dev = torch.device(device)
     backend = backend or ("native" if dev.type == "cuda" else "eager")
@@ -43,15 +45,100 @@ def build_predictor(name: str, device: str = "cuda:0", model_dir: Optional[str] 
         return _make_pipeline(name, device, model_dir, tiny, backend, dtype).predict
     with torch.cuda.device(dev):
         pipe = _make_pipeline(name, device, model_dir, tiny, backend, dtype)
+    if task_batch > 1 and backend == "native" and name in BATCH_FAMILIES:
+        return BatchingPredictor(pipe, dev, task_batch)
+
+    import threading
+    serial = threading.Lock()          # a pipeline's buffers and graphs serve one task at a time
 
     def predict(inp: dict) -> bytes:
-        with torch.cuda.device(dev):
+        with serial, torch.cuda.device(dev):
             return pipe.predict(inp)
 
     predict.pipeline = pipe           # the miner's cost model and the tests reach the pipeline through the callable
     return predict
 
 
+class BatchingPredictor:
+    """Dynamic task batching in front of a pipeline that has ``generate_batch`` (the SD-1.5 family): callers block in
+    ``__call__``; one worker thread per GPU takes the oldest request, adds up to ``task_batch - 1`` queued requests with
+    the same (size, steps, guidance, sampler) — waiting at most ``window_ms`` for them when more solves are known to be
+    on their way — and runs the group as ONE graph replay. Every task's bytes are the ones it gets alone, so batching
+    is invisible on chain; tasks/hour go up because the low-resolution UNet levels are launch-latency bound."""
+
+    def __init__(self, pipe, device=None, task_batch: int = 2, window_ms: float = 2.0, encode=None):
+        import queue
+        import threading
+        self.pipeline, self.device = pipe, device
+        self.task_batch, self.window_s = max(1, int(task_batch)), window_ms / 1e3
+        self._q: "queue.Queue" = queue.Queue()
+        self._encode = encode
+        self.batches = []                                  # sizes of the groups that ran (metrics, tests)
+        self._thread = threading.Thread(target=self._loop, daemon=True)
+        self._thread.start()
+
+    def __call__(self, inp: dict) -> bytes:
+        from concurrent.futures import Future
+        fut: Future = Future()
+        self._q.put((self.pipeline._task_args(inp), fut))
+        return fut.result()
+
+    @staticmethod
+    def _key(t: dict):
+        return (t["width"], t["height"], t["num_inference_steps"], t["guidance_scale"], t["scheduler"])
+
+    def _loop(self) -> None:
+        import contextlib
+        import queue
+        import time
+        held = []                                          # requests taken off the queue that did not fit a group
+        while True:
+            first = held.pop(0) if held else self._q.get()
+            if first is None:
+                return
+            group, rest, deadline, stop = [first], [], None, False
+            while len(group) < self.task_batch:
+                if held:
+                    nxt = held.pop(0)
+                else:
+                    deadline = deadline or (time.monotonic() + self.window_s)
+                    try:
+                        nxt = self._q.get(timeout=max(0.0, deadline - time.monotonic()))
+                    except queue.Empty:
+                        break
+                if nxt is None:
+                    stop = True
+                    break
+                (group if self._key(nxt[0]) == self._key(first[0]) else rest).append(nxt)
+            n = 1 << (len(group).bit_length() - 1)         # group sizes are powers of two: one graph per size in use
+            held = group[n:] + rest + held
+            group = group[:n]
+            self.batches.append(len(group))
+            try:
+                ctx = contextlib.nullcontext()
+                if self.device is not None:
+                    import torch
+                    ctx = torch.cuda.device(self.device)
+                with ctx:
+                    imgs = self.pipeline.generate_batch([t for t, _ in group])
+                if self._encode is None:
+                    from ..codecs.png import encode_png
+                    self._encode = encode_png
+                for (_, fut), img in zip(group, imgs):
+                    fut.set_result(self._encode(img))
+            except BaseException as e:                     # noqa: BLE001 - delivered to every waiting caller
+                for _, fut in group:
+                    if not fut.done():
+                        fut.set_exception(e)
+            if stop:
+                held.append(None)
+
+    def close(self) -> None:
+        self._q.put(None)
+        self._thread.join(5)
+
+
+BATCH_FAMILIES = ("anythingv3",)
 PAIR_FAMILIES = ("anythingv3", "zeroscopev2xl", "damo")
 
 

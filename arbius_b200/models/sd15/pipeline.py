@@ -151,21 +151,35 @@ class SD15Pipeline:
 
     # ---------------- native ----------------
     def _run_native(self, st: dict, sch: Scheduler, g: float) -> None:
-        """Everything between 'ids are on the device' and 'uint8 pixels are on the device'."""
-        dt = self.dtype
+        """Everything between 'ids are on the device' and 'uint8 pixels are on the device', for the ``nb`` tasks of this
+        state at once (UNet batch = [nb negative prompts, nb prompts]). Every split-K choice is the one a lone task
+        gets (``BATCH_SCALE``), all other kernels are per-sample, so a task's bytes do not depend on its batch mates."""
+        import sys
+        from fractions import Fraction
+        gemm_mod = sys.modules["arbius_b200.ops.gemm"]
+        nb = st["nb"]
+        if nb > 1:
+            gemm_mod.BATCH_SCALE = Fraction(1, nb)
+        try:
+            self._run_native_body(st, sch, g, nb)
+        finally:
+            if nb > 1:
+                gemm_mod.BATCH_SCALE = 1
+
+    def _run_native_body(self, st: dict, sch: Scheduler, g: float, nb: int) -> None:
         ctx = self.clip.forward(st["ids"])
         kvs = self.unet.precompute_context(ctx)
-        temb = self.unet.time_projections(st["tvec"])          # [2*steps, sum(Cout)]
+        temb = self.unet.time_projections(st["tvec"])          # [2*nb*steps, sum(Cout)]
         f = st["f32"]
         ops.lincomb(f["x"], [(sch.init_noise_sigma, st["noise0"])])
         n_steps = len(sch.timesteps)
         for i in range(n_steps):
             s_in = sch.input_scale(i)
             for b in range(2):
-                ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=s_in)
+                ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b * nb:(b + 1) * nb], m_scale=s_in)
             if self.cfgp is None:
-                e = self.unet.forward(st["xin"], temb[2 * i:2 * i + 2], kvs)
-                ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
+                e = self.unet.forward(st["xin"], temb[2 * nb * i:2 * nb * (i + 1)], kvs)
+                ops.cfg_step(e[nb:], e[:nb], None, g=g, eps_out=f["eps"])
             else:
                 self._cfg_parallel_step(st, i, temb, kvs, g)
             for dst, terms in sch.plan(i):
@@ -198,7 +212,8 @@ class SD15Pipeline:
                                          slot.numel(), g, 0.0, 1.0, 0.0, 0.0, ops.native.dtype_code(slot.dtype),
                                          ops.native.stream_ptr()), "ab_cfg_step")
 
-    def _state(self, key, width, height, steps, g, sched_name) -> dict:
+    def _state(self, key, width, height, steps, g, sched_name, nb: int = 1) -> dict:
+        assert nb == 1 or self.cfgp is None, "a task batch and guidance parallelism do not combine"
         st = self._graphs.get(key)
         if st is not None:
             return st
@@ -207,17 +222,17 @@ class SD15Pipeline:
         sch = make_scheduler(sched_name)
         sch.set_timesteps(steps)
         names = {"x", "eps", "tmp"} | set(sch.history)
-        st = dict(sch=sch,
-                  ids=torch.zeros((2, self.tokenizer.max_len), dtype=torch.int64, device=dev),
-                  ids_host=torch.zeros((2, self.tokenizer.max_len), dtype=torch.int64).pin_memory(),
-                  tvec=torch.tensor([t for t in sch.timesteps for _ in range(2)], dtype=torch.float32, device=dev),
-                  noise0=torch.zeros((1, h, w, 4), dtype=torch.float32, device=dev),
-                  noise=[torch.zeros((1, h, w, 4), dtype=torch.float32, device=dev) for _ in range(len(sch.timesteps))]
+        st = dict(sch=sch, nb=nb,
+                  ids=torch.zeros((2 * nb, self.tokenizer.max_len), dtype=torch.int64, device=dev),
+                  ids_host=torch.zeros((2 * nb, self.tokenizer.max_len), dtype=torch.int64).pin_memory(),
+                  tvec=torch.tensor([t for t in sch.timesteps for _ in range(2 * nb)], dtype=torch.float32, device=dev),
+                  noise0=torch.zeros((nb, h, w, 4), dtype=torch.float32, device=dev),
+                  noise=[torch.zeros((nb, h, w, 4), dtype=torch.float32, device=dev) for _ in range(len(sch.timesteps))]
                   if sch.stochastic else [],
-                  f32={n: torch.zeros((1, h, w, 4), dtype=torch.float32, device=dev) for n in names},
-                  xin=torch.zeros((2, h, w, 4), dtype=dt, device=dev),
-                  lat=torch.zeros((1, h, w, 4), dtype=dt, device=dev),
-                  out_host=torch.zeros((height, width, 3), dtype=torch.uint8).pin_memory(),
+                  f32={n: torch.zeros((nb, h, w, 4), dtype=torch.float32, device=dev) for n in names},
+                  xin=torch.zeros((2 * nb, h, w, 4), dtype=dt, device=dev),
+                  lat=torch.zeros((nb, h, w, 4), dtype=dt, device=dev),
+                  out_host=torch.zeros((nb, height, width, 3), dtype=torch.uint8).pin_memory(),
                   graph=None, launches=0)
         if self.cfgp is not None:
             st["ex"], st["ex_off"] = self.cfgp.alloc((2, 1, h, w, 4), dt)      # same offset on both ranks
@@ -239,27 +254,37 @@ class SD15Pipeline:
         return st
 
     def _generate_native(self, ids, width, height, steps, g, sched_name, seed) -> np.ndarray:
-        key = (width, height, steps, float(g), sched_name)
-        st = self._state(key, width, height, steps, g, sched_name)
+        return self._generate_native_batch([ids], width, height, steps, g, sched_name, [seed])[0]
+
+    def _generate_native_batch(self, ids_list, width, height, steps, g, sched_name, seeds) -> np.ndarray:
+        """``nb`` tasks that share (size, steps, guidance, sampler) in one graph replay -> uint8 [nb, H, W, 3]. Rows of
+        the UNet batch: the nb negative prompts, then the nb prompts."""
+        nb = len(ids_list)
+        key = (width, height, steps, float(g), sched_name) + ((nb,) if nb > 1 else ())
+        st = self._state(key, width, height, steps, g, sched_name, nb)
         sch = st["sch"]
-        st["ids_host"].copy_(ids)
+        for t, ids in enumerate(ids_list):
+            st["ids_host"][t].copy_(ids[0])
+            st["ids_host"][nb + t].copy_(ids[1])
         st["ids"].copy_(st["ids_host"], non_blocking=True)
-        self.h2d_bytes = ids.numel() * 8
+        self.h2d_bytes = st["ids_host"].numel() * 8
         h, w = height // self.vae_scale, width // self.vae_scale
         lib = ops.native.load()
         n = h * w * 4
-        ops.native.check(lib.ab_philox_normal(st["noise0"].data_ptr(), n, seed, NOISE_STREAM_INIT, 0,
-                                              ops.native.stream_ptr()), "philox")
-        for i, nb in enumerate(st["noise"]):
-            ops.native.check(lib.ab_philox_normal(nb.data_ptr(), n, seed, 1 + i, 0, ops.native.stream_ptr()), "philox")
+        for t, seed in enumerate(seeds):
+            ops.native.check(lib.ab_philox_normal(st["noise0"][t].data_ptr(), n, seed, NOISE_STREAM_INIT, 0,
+                                                  ops.native.stream_ptr()), "philox")
+            for i, nbuf in enumerate(st["noise"]):
+                ops.native.check(lib.ab_philox_normal(nbuf[t].data_ptr(), n, seed, 1 + i, 0, ops.native.stream_ptr()),
+                                 "philox")
         if st["graph"] is not None:
             st["graph"].replay()
-            self.last_launches = st["launches"] + 1 + len(st["noise"])
+            self.last_launches = st["launches"] + nb * (1 + len(st["noise"]))
         else:
             n0 = ops.native.launch_count()
             self._run_native(st, sch, g)
-            self.last_launches = ops.native.launch_count() - n0 + 1 + len(st["noise"])
-        st["out_host"].copy_(st["u8"][0], non_blocking=True)
+            self.last_launches = ops.native.launch_count() - n0 + nb * (1 + len(st["noise"]))
+        st["out_host"].copy_(st["u8"], non_blocking=True)
         torch.cuda.current_stream().synchronize()
         self.d2h_bytes = st["out_host"].numel()
         return st["out_host"].numpy().copy()
@@ -268,29 +293,50 @@ class SD15Pipeline:
     def predict(self, inp: dict) -> bytes:
         """Hydrated template input (+ integer ``seed``) -> PNG bytes of ``out-1.png``."""
         from ...codecs.png import encode_png
-        img = self.generate(prompt=inp["prompt"], negative_prompt=inp.get("negative_prompt", "") or "",
-                            width=int(inp.get("width", 768)), height=int(inp.get("height", 768)),
-                            num_inference_steps=int(inp.get("num_inference_steps", 20)),
-                            guidance_scale=float(inp.get("guidance_scale", 12)),
-                            scheduler=inp.get("scheduler", "DPMSolverMultistep"), seed=int(inp.get("seed", 0)))
-        return encode_png(img)
+        return encode_png(self.generate(**self._task_args(inp)))
 
-    def predict_many(self, inputs) -> list:
+    @staticmethod
+    def _task_args(inp: dict) -> dict:
+        return dict(prompt=inp["prompt"], negative_prompt=inp.get("negative_prompt", "") or "",
+                    width=int(inp.get("width", 768)), height=int(inp.get("height", 768)),
+                    num_inference_steps=int(inp.get("num_inference_steps", 20)),
+                    guidance_scale=float(inp.get("guidance_scale", 12)),
+                    scheduler=inp.get("scheduler", "DPMSolverMultistep"), seed=int(inp.get("seed", 0)))
+
+    def generate_batch(self, tasks: List[dict]) -> np.ndarray:
+        """Tasks (``_task_args`` dicts) that agree on size, steps, guidance and sampler -> uint8 [n, H, W, 3] from ONE
+        graph replay. Each image has the bytes ``generate`` gives that task alone."""
+        a = tasks[0]
+        if self.backend != "native" or self.cfgp is not None or len(tasks) == 1:
+            return np.stack([self.generate(**t) for t in tasks])
+        ids = [self._token_ids(t["prompt"], t["negative_prompt"]) for t in tasks]
+        return self._generate_native_batch(ids, a["width"], a["height"], a["num_inference_steps"], a["guidance_scale"],
+                                           a["scheduler"], [t["seed"] for t in tasks])
+
+    def predict_many(self, inputs, task_batch: int = 1) -> list:
         """A queue of hydrated inputs -> PNG bytes in order. The PNG encode of task i (host, native deflate, GIL
         released) runs on a worker thread while the GPU replays the graph of task i+1, so the end-to-end rate
-        approaches the device rate; every task still does its own pinned H2D of token ids and D2H of pixels."""
+        approaches the device rate; every task still does its own pinned H2D of token ids and D2H of pixels.
+        ``task_batch`` > 1 runs up to that many consecutive tasks with equal (size, steps, guidance, sampler) in one
+        replay: the low-resolution UNet levels are launch-latency bound at batch 2, so tasks/hour go up while each
+        task's latency grows; the bytes per task are unchanged."""
         from concurrent.futures import ThreadPoolExecutor
 
         from ...codecs.png import encode_png
+        tasks = [self._task_args(inp) for inp in inputs]
+        shape_key = lambda t: (t["width"], t["height"], t["num_inference_steps"], t["guidance_scale"], t["scheduler"])
         with ThreadPoolExecutor(max_workers=2) as pool:
             futs = []
-            for inp in inputs:
-                img = self.generate(prompt=inp["prompt"], negative_prompt=inp.get("negative_prompt", "") or "",
-                                    width=int(inp.get("width", 768)), height=int(inp.get("height", 768)),
-                                    num_inference_steps=int(inp.get("num_inference_steps", 20)),
-                                    guidance_scale=float(inp.get("guidance_scale", 12)),
-                                    scheduler=inp.get("scheduler", "DPMSolverMultistep"), seed=int(inp.get("seed", 0)))
-                futs.append(pool.submit(encode_png, img))
+            i = 0
+            while i < len(tasks):
+                j = i + 1
+                while j < len(tasks) and j - i < task_batch and shape_key(tasks[j]) == shape_key(tasks[i]):
+                    j += 1
+                if j - i < task_batch:
+                    j = i + 1                          # partial groups run singly: one graph per batch size in use
+                imgs = self.generate_batch(tasks[i:j])
+                futs += [pool.submit(encode_png, img) for img in imgs]
+                i = j
             return [f.result() for f in futs]
 
 

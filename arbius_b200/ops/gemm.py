@@ -29,7 +29,12 @@ RECORD: Optional[list] = None      # set to a list to log every (key, call kwarg
 # Canonical-batch multiplier: when one task's batch is split over GPUs (classifier-free-guidance parallelism: each GPU
 # runs one of the two UNet branches) every tiling decision that changes the summation order (split-K) must be the one
 # the undivided batch would get, or the bytes would depend on the GPU count. The models set this around their calls.
+# A Fraction 1/n is set while n independent tasks share one batch: each task then gets the choices it gets alone.
 BATCH_SCALE = 1
+
+
+def _canon(m: int) -> int:
+    return int(m * BATCH_SCALE)
 
 
 def tuned_config(key: str):
@@ -118,14 +123,14 @@ def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
     a.ldr = res.stride(0) if res is not None else 0
     a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = (k1 + k2 + 63) // 64
-    key = f"{'geglu' if geglu else 'lin'}:{m * BATCH_SCALE}:{n}:{k1 + k2}"
+    key = f"{'geglu' if geglu else 'lin'}:{_canon(m)}:{n}:{k1 + k2}"
     if RECORD is not None:
         RECORD.append(key)
     cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
     if cfg is not None:
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:
-        a.splitk = splitk if splitk > 0 else auto_splitk(m * BATCH_SCALE, n, kc)
+        a.splitk = splitk if splitk > 0 else auto_splitk(_canon(m), n, kc)
     if a.splitk > 1:
         a.workspace = _workspace(a.splitk * m * n * 4, x.device).data_ptr()
     native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm")
@@ -154,14 +159,14 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     a.block_n = block_n
     a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = 9 * (c1 + c2) // 64
-    key = f"conv:{b * BATCH_SCALE}x{h}x{wd}:{n}:{c1 + c2}"
+    key = f"conv:{_canon(b)}x{h}x{wd}:{n}:{c1 + c2}"
     if RECORD is not None:
         RECORD.append(key)
     cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
     if cfg is not None:
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:
-        a.splitk = splitk if splitk > 0 else auto_splitk(a.M * BATCH_SCALE, n, kc)
+        a.splitk = splitk if splitk > 0 else auto_splitk(_canon(a.M), n, kc)
     if a.splitk > 1:
         a.workspace = _workspace(a.splitk * a.M * n * 4, x.device).data_ptr()
     native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm(conv)")
@@ -205,7 +210,7 @@ def conv_temporal(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.
     a.conv, a.nimg, a.H, a.W = 2, b, f, hw
     a.act, a.out_scale = ACT[act], 1.0
     a.dtype = native.dtype_code(x.dtype)
-    key = f"tconv:{b * BATCH_SCALE}x{f}x{hw}:{n}:{c}"
+    key = f"tconv:{_canon(b)}x{f}x{hw}:{n}:{c}"
     if RECORD is not None:
         RECORD.append(key)
     cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
@@ -213,7 +218,7 @@ def conv_temporal(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:
         a.block_n = block_n
-        a.splitk = splitk if splitk > 0 else auto_splitk(a.M * BATCH_SCALE, n, 3 * c // 64)
+        a.splitk = splitk if splitk > 0 else auto_splitk(_canon(a.M), n, 3 * c // 64)
     if a.splitk > 1:
         a.workspace = _workspace(a.splitk * a.M * n * 4, x.device).data_ptr()
     native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm(temporal conv)")

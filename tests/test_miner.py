@@ -327,3 +327,54 @@ def test_expretry_returns_none_after_exhaustion():
     waits = []
     assert expretry(flaky, sleep=waits.append) == 42 and waits == [1.0, 1.5]
     assert expretry(lambda: 1 / 0, tries=2, sleep=lambda s: None) is None
+
+
+def test_task_slots_let_a_batching_predictor_merge_solves():
+    """slots=2: two solves are admitted per GPU and the batching predictor runs them as one group; subsets of two GPUs
+    still need both GPUs idle."""
+    from arbius_b200.models.registry import BatchingPredictor
+    pl = SubsetPlanner(2, slots=2)
+    assert [pl.acquire(1) for _ in range(5)] == [(0,), (1,), (0,), (1,), None]
+    assert pl.largest_free_aligned() == 0 and pl.free_count() == 0
+    pl.release((0,)); pl.release((0,))
+    assert pl.largest_free_aligned() == 1 and pl.acquire(2) is None          # GPU 1 still has work
+    pl.release((1,)); pl.release((1,))
+    assert pl.acquire(2) == (0, 1) and pl.acquire(1) is None
+    pl.release((0, 1))
+    assert pl.free_count() == 4
+
+    class FakePipe:
+        groups = []
+
+        @staticmethod
+        def _task_args(inp):
+            return dict(width=64, height=64, num_inference_steps=int(inp.get("num_inference_steps", 2)),
+                        guidance_scale=7.0, scheduler="x", seed=inp["seed"])
+
+        def generate_batch(self, tasks):
+            self.groups.append([t["seed"] for t in tasks])
+            time.sleep(0.02)
+            return [bytes([t["seed"]]) for t in tasks]
+    bp = BatchingPredictor(FakePipe(), None, task_batch=2, window_ms=200.0, encode=lambda img: FIXED_PNG + img)
+    eng, node, mid, _ = _setup()
+    model = node.models[0]
+    ml = NativeBackend({mid: [bp]}, slots=2)
+    out = {}
+    ths = [threading.Thread(target=lambda s=s: out.__setitem__(s, ml.getfiles(model, "0x0", {"seed": s}, gpus=(0,))))
+           for s in (1, 2, 3)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join(10)
+    assert {s: v["out-1.png"] for s, v in out.items()} == {s: FIXED_PNG + bytes([s]) for s in (1, 2, 3)}
+    assert sorted(len(g) for g in FakePipe.groups) == [1, 2]                    # two merged, the third ran after them
+    # a request with other settings is not merged into the group
+    FakePipe.groups.clear()
+    ths = [threading.Thread(target=lambda kw=kw: ml.getfiles(model, "0x0", kw, gpus=(0,)))
+           for kw in ({"seed": 7}, {"seed": 8, "num_inference_steps": 5})]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join(10)
+    assert sorted(FakePipe.groups) == [[7], [8]]
+    bp.close()

@@ -128,3 +128,21 @@ def test_native_pipeline_matches_eager_and_is_bit_reproducible(sched):
     kw2 = dict(kw, seed=4242)
     assert (nat.generate(**kw2) != a).any()
     assert nat.last_launches > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sched", ["DPMSolverMultistep", "K_EULER_ANCESTRAL"])
+def test_task_batch_gives_each_task_the_bytes_it_gets_alone(sched):
+    """Independent tasks that share one graph replay (UNet batch 2*n) must come out byte for byte as when they run alone:
+    split-K choices are pinned to the lone task's, everything else is per-sample."""
+    pipe = SD15Pipeline(SD15Config.tiny(), backend="native", device="cuda", dtype=torch.float16, use_graph=True)
+    inputs = [{"prompt": f"prompt number {s}", "negative_prompt": "blurry" if s % 2 else "", "width": 64, "height": 64,
+               "num_inference_steps": 3, "guidance_scale": 7.5, "scheduler": sched, "seed": 100 + s} for s in range(5)]
+    alone = [pipe.predict(i) for i in inputs]
+    assert len(set(alone)) == 5
+    for tb in (2, 4):
+        assert pipe.predict_many(inputs, task_batch=tb) == alone, f"task_batch={tb}"
+    # a task with different settings in the middle of the queue breaks the group, not the result
+    odd = dict(inputs[1], num_inference_steps=2)
+    mixed = pipe.predict_many([inputs[0], odd, inputs[2], inputs[3]], task_batch=2)
+    assert mixed[0] == alone[0] and mixed[2] == alone[2] and mixed[3] == alone[3] and mixed[1] == pipe.predict(odd)
