@@ -93,7 +93,7 @@ def main() -> int:
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--latency-mode", action="store_true",
                     help="with >= 2 GPUs also time guidance-parallel pairs (one task over two GPUs) and add 'latency_mode'")
-    ap.add_argument("--task-batch", type=int, default=1,
+    ap.add_argument("--task-batch", type=int, default=4,
                     help="independent tasks per graph replay (anythingv3 native only); bytes per task do not change")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -211,6 +211,20 @@ def main() -> int:
     launches = counted[0] if args.impl == "native" else 0
     eager_launches = (ops.native.launch_count() - n0) if args.impl == "native" else 0
 
+    # ---- the same K tasks one per replay (lowest latency per task), reported next to the batched headline ----
+    single = None
+    if TB > 1:
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for i in range(K):
+            pipe.generate(seed=2000 + rank * 1000 + i, **base)
+        s1.record()
+        barrier()
+        single_ms = reduce_max(s0.elapsed_time(s1)) / K
+        single = {"task_batch": 1, "ms_per_task": round(single_ms, 3), "p50_latency_ms": round(single_ms, 3),
+                  "tasks_per_hour": round(world / (single_ms / 1e3) * 3600.0, 2)}
+
     # ---- end-to-end: public API predict() -> PNG bytes (+ CID), pinned H2D in, D2H out, every task ----
     barrier()
     t0 = time.perf_counter()
@@ -251,6 +265,10 @@ def main() -> int:
                 "last_cid": cid},
         "gpu_launches": int(launches or eager_launches),
     }
+    if single is not None:
+        out["single_task"] = single
+        out["config"]["batching"] = (f"{TB} independent tasks per CUDA-graph replay (UNet batch {2 * TB}); each task's bytes "
+                                     "equal the ones it gets alone (tests/test_sd15.py)")
     if args.latency_mode and world >= 2 and world % 2 == 0 and args.impl == "native" and not args.model.startswith("kandinsky"):
         # Optional second measurement: the same tasks with guidance parallelism (pairs of GPUs share one task: lower
         # latency, byte-identical output). world/2 tasks are in flight at a time.

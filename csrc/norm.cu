@@ -41,6 +41,10 @@ struct GnParams {
     int act;
     int ss;                  // row stride (elements) of scale/shift
     int apply_nb;            // batches of GN_APPLY_ROWS rows per apply thread (amortises the affine set-up on big maps)
+    // sharded tensors (one sample spread over GPUs by rows): this GPU holds canonical shards
+    // [shard_base, shard_base + ns_local) of every sample; hw is then the LOCAL row count. ns_local == 0: all 8.
+    int ns_local, shard_base;
+    long long y_bs;          // elements between consecutive samples of y (0: hw * C)
 };
 
 // workspace layout: counters (n * 4 B, padded to 256) | stats (n*groups*8 B, padded to 256) | partials
@@ -103,8 +107,9 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
     const int n = blockIdx.z, shard = blockIdx.y, sub = blockIdx.x;
     pdl_wait();
     pdl_launch_dependents();
-    const int s_begin = static_cast<int>((static_cast<long long>(shard) * p.hw) / GN_SHARDS);
-    const int s_end = static_cast<int>((static_cast<long long>(shard + 1) * p.hw) / GN_SHARDS);
+    const int ns = p.ns_local > 0 ? p.ns_local : GN_SHARDS;
+    const int s_begin = static_cast<int>((static_cast<long long>(shard) * p.hw) / ns);
+    const int s_end = static_cast<int>((static_cast<long long>(shard + 1) * p.hw) / ns);
     const int len = s_end - s_begin;
     const int r0 = s_begin + static_cast<int>((static_cast<long long>(sub) * len) / p.sub);
     const int r1 = s_begin + static_cast<int>((static_cast<long long>(sub + 1) * len) / p.sub);
@@ -164,7 +169,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const GnParams p) 
     }
     __syncthreads();
     gn_block_moments(s_sum, s_sq, RL, C, cpg, p.groups, r1 - r0,
-                     p.partials + ((static_cast<long long>(n) * GN_SHARDS + shard) * p.sub + sub) * p.groups);
+                     p.partials + ((static_cast<long long>(n) * GN_SHARDS + p.shard_base + shard) * p.sub + sub) * p.groups);
+    if (p.ns_local > 0) return;   // sharded: gn_finalize_sharded_kernel merges every GPU's partials after the barrier
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -221,7 +227,7 @@ __global__ void __launch_bounds__(GN_APPLY_THREADS, 2) gn_apply_kernel(const GnP
     const T* beta = reinterpret_cast<const T*>(p.beta);
     const T* scale = reinterpret_cast<const T*>(p.scale);
     const T* shift = reinterpret_cast<const T*>(p.shift);
-    T* y = reinterpret_cast<T*>(p.y) + static_cast<long long>(n) * p.hw * C;
+    T* y = reinterpret_cast<T*>(p.y) + (p.y_bs > 0 ? static_cast<long long>(n) * p.y_bs : static_cast<long long>(n) * p.hw * C);
     for (int pass = 0; pass < passes; ++pass) {
         const int vc = pass * cols + threadIdx.x % cols;
         if (vc >= ncol) continue;
@@ -275,6 +281,34 @@ __global__ void __launch_bounds__(GN_APPLY_THREADS, 2) gn_apply_kernel(const GnP
             *reinterpret_cast<uint4*>(y + static_cast<long long>(r) * C + c) = pack8<T>(o);
         }
         }   // batches
+    }
+}
+
+// Sharded GroupNorm, second step: every GPU merges ALL partial moments — its own and, through peer pointers, the other
+// GPUs' — in the canonical order of gn_stats_kernel's last block (blocks of a shard in index order, then shards 0..7),
+// so each GPU ends up with the statistics the undivided tensor gives, bit for bit. One block per sample.
+struct GnShardSrcs { const float4* part[GN_SHARDS]; };   // partial-moment array of the GPU that owns canonical shard i
+__global__ void __launch_bounds__(GN_THREADS) gn_finalize_sharded_kernel(const GnParams p, const GnShardSrcs srcs) {
+    __shared__ GnMoments shard_mom[GN_SHARDS][GN_MAX_GROUPS + 1];
+    const int n = blockIdx.x;
+    for (int idx = threadIdx.x; idx < GN_SHARDS * p.groups; idx += GN_THREADS) {
+        const int sh = idx / p.groups, g = idx % p.groups;
+        const volatile float4* part = srcs.part[sh] + static_cast<long long>(n) * GN_SHARDS * p.sub * p.groups;
+        GnMoments acc{0.f, 0.f, 0.f};
+        for (int sb = 0; sb < p.sub; ++sb) {
+            const volatile float4* q4 = &part[(sh * p.sub + sb) * p.groups + g];
+            acc = gn_merge(acc, GnMoments{q4->x, q4->y, q4->z});
+        }
+        shard_mom[sh][g] = acc;
+    }
+    __syncthreads();
+    if (threadIdx.x < p.groups) {
+        const int g = threadIdx.x;
+        GnMoments acc = shard_mom[0][g];
+#pragma unroll
+        for (int sh = 1; sh < GN_SHARDS; ++sh) acc = gn_merge(acc, shard_mom[sh][g]);
+        const float var = acc.m2 / acc.cnt;
+        p.stats[n * p.groups + g] = make_float2(acc.mean, rsqrtf(var + p.eps));
     }
 }
 
@@ -635,6 +669,75 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
         AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     }
     AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(2);
+    return 0;
+}
+
+// Sharded GroupNorm (one sample's rows spread over 2, 4 or 8 GPUs, e.g. video frames): two entry points with the GPUs'
+// barrier between them.
+//   ab_groupnorm_sharded_stats : partial moments of this GPU's canonical shards -> `partials_out` (peer-visible memory,
+//                                layout [n][8][sub][groups] float4, only this GPU's shard rows are written)
+//   ab_groupnorm_sharded_apply : merge all GPUs' partials (`part_srcs[i]` = array of the GPU owning shard i) in canonical
+//                                order, then normalise the local rows. `a->partials` is the usual local workspace.
+// a->hw is the LOCAL row count; hw_global = a->hw * world fixes the canonical sub-block count.
+extern "C" int ab_groupnorm_sharded_stats(const ab_groupnorm_args* a, int world, int rank, void* partials_out, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && a->x && partials_out, "null pointer");
+    AB_REQUIRE(world == 2 || world == 4 || world == 8, "world must be 2, 4 or 8");
+    const int C = a->c1 + a->c2;
+    AB_REQUIRE(a->n > 0 && a->hw > 0 && a->c1 > 0 && a->c1 % 8 == 0 && a->c2 % 8 == 0, "bad shape");
+    AB_REQUIRE(a->groups > 0 && a->groups <= GN_MAX_GROUPS && C % a->groups == 0, "bad group count");
+    const int ns = GN_SHARDS / world;
+    AB_REQUIRE(a->hw % ns == 0, "local rows must split evenly into this GPU's canonical shards");
+    GnParams p{};
+    p.x = a->x; p.x2 = a->x2;
+    p.partials = reinterpret_cast<float4*>(partials_out);
+    p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
+    p.sub = gn_sub_blocks(a->hw * world);
+    p.ns_local = ns; p.shard_base = rank * ns;
+    const int ncol = C / 8;
+    const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
+    const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
+    AB_REQUIRE(smem <= 48 * 1024, "channel count too large for the stats kernel");
+    dim3 grid(p.sub, ns, a->n);
+    if (a->dtype == AB_BF16) AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__nv_bfloat16>, grid, dim3(GN_THREADS), smem, stream, p));
+    else AB_CHECK_CUDA(launch_pdl(gn_stats_kernel<__half>, grid, dim3(GN_THREADS), smem, stream, p));
+    ab_count_launch(1);
+    return 0;
+}
+
+extern "C" int ab_groupnorm_sharded_apply(const ab_groupnorm_args* a, int world, void* const* part_srcs, long long y_batch_stride,
+                                          void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && a->x && a->y && a->partials && part_srcs, "null pointer");
+    AB_REQUIRE(world == 2 || world == 4 || world == 8, "world must be 2, 4 or 8");
+    const int C = a->c1 + a->c2;
+    AB_REQUIRE(a->groups > 0 && a->groups <= GN_MAX_GROUPS && C % a->groups == 0, "bad group count");
+    GnParams p{};
+    p.x = a->x; p.x2 = a->x2; p.y = a->y; p.gamma = a->gamma; p.beta = a->beta; p.scale = a->scale; p.shift = a->shift;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(a->partials);
+    p.stats = reinterpret_cast<float2*>(ws + gn_counters_bytes(a->n));
+    p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
+    p.sub = gn_sub_blocks(a->hw * world);
+    p.eps = a->eps; p.act = a->act; p.ss = a->ss_stride > 0 ? a->ss_stride : C;
+    p.y_bs = y_batch_stride;
+    GnShardSrcs srcs;
+    const int ns = GN_SHARDS / world;
+    for (int sh = 0; sh < GN_SHARDS; ++sh) {
+        AB_REQUIRE(part_srcs[sh / ns], "null partials source");
+        srcs.part[sh] = reinterpret_cast<const float4*>(part_srcs[sh / ns]);
+    }
+    gn_finalize_sharded_kernel<<<a->n, GN_THREADS, 0, stream>>>(p, srcs);
+    AB_CHECK_CUDA(cudaGetLastError());
+    const int ncol = C / 8;
+    const int apply_cols = ncol < GN_APPLY_THREADS ? ncol : GN_APPLY_THREADS;
+    p.apply_nb = static_cast<long long>(a->n) * a->hw >= 65536 ? 4 : 1;
+    const int apply_rows = (GN_APPLY_THREADS / apply_cols) * GN_APPLY_ROWS * p.apply_nb;
+    dim3 blocks((a->hw + apply_rows - 1) / apply_rows, a->n);
+    if (a->dtype == AB_BF16) AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
+    else AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     ab_count_launch(2);
     return 0;
 }
