@@ -193,3 +193,53 @@ def build_pair_predictor(name: str, devices=(0, 1), model_dir: Optional[str] = N
 
     predict.pipelines = pipes
     return predict
+
+
+FRAME_FAMILIES = ("zeroscopev2xl", "damo")
+
+
+def build_frame_parallel_predictor(name: str, devices=(0, 1), model_dir: Optional[str] = None, tiny: bool = False,
+                                   dtype=None, heap_bytes: Optional[int] = None) -> Callable[[dict], bytes]:
+    """One text-to-video task over 2, 4 or 8 GPUs of this process: sequence (frame) parallelism — each device denoises
+    and decodes F/P frames, the temporal layers cross devices through peer memory (parallel/frame_shard.py), and the
+    clip has the bytes of the single-GPU pipeline. The first device assembles and returns the MP4."""
+    import threading
+
+    import torch
+
+    from ..parallel.symm import PeerHeap
+    from .video.pipeline import TextToVideoConfig, TextToVideoPipeline
+    if name not in FRAME_FAMILIES:
+        raise ValueError(f"{name!r} has no frame-parallel form; choices: {FRAME_FAMILIES}")
+    assert len(devices) in (2, 4, 8)
+    dtype = dtype or torch.float16
+    heaps = PeerHeap.local_group(heap_bytes or ((256 << 20) if tiny else (3 << 30)), devices)
+    cfg = TextToVideoConfig.tiny() if tiny else (TextToVideoConfig.zeroscope_xl() if name == "zeroscopev2xl"
+                                                  else TextToVideoConfig.damo())
+    pipes = []
+    for d, heap in zip(devices, heaps):
+        with torch.cuda.device(d):
+            pipes.append(TextToVideoPipeline(cfg, backend="native", device=f"cuda:{d}", dtype=dtype, model_dir=model_dir,
+                                             family=name, frame_parallel=heap))
+
+    def predict(inp: dict) -> bytes:
+        out = [None] * len(devices)
+
+        def run(i: int) -> None:
+            try:
+                with torch.cuda.device(devices[i]):
+                    out[i] = pipes[i].predict(dict(inp))
+            except BaseException as e:                      # noqa: BLE001 - re-raised on the calling thread
+                out[i] = e
+        threads = [threading.Thread(target=run, args=(i,)) for i in range(len(devices))]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        for o in out:
+            if isinstance(o, BaseException):
+                raise o
+        return out[0]
+
+    predict.pipelines = pipes
+    return predict

@@ -30,11 +30,19 @@ class _TemporalConv:
             self.stages.append((g(f"{name}.0.weight"), g(f"{name}.0.bias"),
                                 ops.pack_temporal_conv_weight(g(f"{name}.{ci}.weight")), g(f"{name}.{ci}.bias")))
 
+    shard = None                       # a parallel.frame_shard.FrameShard when the frames are spread over GPUs
+
     def __call__(self, x: torch.Tensor) -> torch.Tensor:
         """x [B, F, H, W, C]"""
         b, f, h, w, c = x.shape
         y = x.view(b, f, h * w, c)
         idt = y
+        if self.shard is not None:
+            for i, (nw, nb, cw, cb) in enumerate(self.stages):
+                pad = self.shard.groupnorm(y, nw, nb, self.groups, 1e-5, "silu", padded_parity=i & 1)
+                self.shard.exchange_halos(pad, i & 1)
+                y = ops.conv_temporal(pad, cw, cb, residual=idt if i == 3 else None, halo=True)
+            return y.view(b, f, h, w, c)
         for i, (nw, nb, cw, cb) in enumerate(self.stages):
             y = ops.groupnorm(y, nw, nb, self.groups, 1e-5, "silu")           # stats over (F, H, W) per sample
             y = ops.conv_temporal(y, cw, cb, residual=idt if i == 3 else None)
@@ -112,9 +120,15 @@ class _TemporalTransformer:
         self.inner = self.piw.shape[0]
         self.blk = _Block(sd, p + "transformer_blocks.0.", dtype, device, double_self=True)
 
+    shard = None                       # see _TemporalConv.shard
+
     def _self_attn(self, t, ln, wqkv, wo, bo, b, f, hw):
         c = self.inner
         n = ops.layernorm(t, *ln)
+        if self.shard is not None:
+            ops.gemm(n, wqkv, out=self.shard.qkv_buffer(b, hw, 3 * c))
+            a = self.shard.temporal_attention(b, hw, self.heads, c)
+            return ops.gemm(a, wo, bo, residual=t)
         qkv = ops.gemm(n, wqkv).view(b, f, hw, 3 * c)
         q, k, v = (qkv[..., i * c:(i + 1) * c] for i in range(3))
         a = temporal_attn(q, k, v, self.heads)
@@ -124,7 +138,10 @@ class _TemporalTransformer:
         b, f, hh, ww, c = x.shape
         hw = hh * ww
         B = self.blk
-        t = ops.groupnorm(x.view(b, f * hw, c), self.nw, self.nb, self.groups, 1e-6, None)     # over (F, H, W)
+        if self.shard is not None:
+            t = self.shard.groupnorm(x.view(b, f * hw, c), self.nw, self.nb, self.groups, 1e-6, None)
+        else:
+            t = ops.groupnorm(x.view(b, f * hw, c), self.nw, self.nb, self.groups, 1e-6, None)     # over (F, H, W)
         t = ops.gemm(t.view(b * f * hw, c), self.piw, self.pib)
         t = self._self_attn(t, B.ln1, B.wqkv1, B.wo1, B.bo1, b, f, hw)
         t = self._self_attn(t, B.ln2, B.wqkv2, B.wo2, B.bo2, b, f, hw)
@@ -199,6 +216,14 @@ class NativeUNet3D:
 
     def precompute_context(self, ctx: torch.Tensor) -> List[torch.Tensor]:
         return [t.context_kv(ctx) for t in self.spatial]
+
+    def set_frame_shard(self, shard) -> None:
+        """Run the temporal layers across the ranks of ``shard`` (parallel/frame_shard.py); None: single GPU."""
+        mods = [self.transformer_in, self.mid["tatt"]] + self.mid["tc"]
+        for blk in self.down + self.up:
+            mods += blk["tc"] + (blk["tatt"] or [])
+        for m in mods:
+            m.shard = shard
 
     def time_projections(self, t: torch.Tensor, frames: int) -> torch.Tensor:
         """t [B] -> [B*F, sum(Cout)]: one row per (sample, frame) image, as the spatial resnets index it."""

@@ -52,13 +52,20 @@ class TextToVideoConfig:
 class TextToVideoPipeline:
     def __init__(self, cfg: TextToVideoConfig, backend: str = "native", device: str = "cuda", dtype=torch.float16,
                  seed: int = 0, model_dir: Optional[str] = None, family: str = "zeroscopev2xl", use_graph: bool = True,
-                 cfg_parallel=None):
+                 cfg_parallel=None, frame_parallel=None):
         """``cfg_parallel``: a 2-rank ``PeerHeap`` — guidance parallelism as in ``SD15Pipeline``: each GPU runs one
         classifier-free-guidance branch of every UNet3D step and the predictions are exchanged through peer memory.
-        The video kernels are large, so one task takes close to half the single-GPU time, with identical bytes."""
+        The video kernels are large, so one task takes close to half the single-GPU time, with identical bytes.
+        ``frame_parallel``: a 2/4/8-rank ``PeerHeap`` — sequence parallelism (parallel/frame_shard.py): every rank
+        denoises and decodes F/P frames of ONE task; temporal GroupNorm, temporal conv and temporal attention cross
+        ranks through peer memory in the single-GPU kernels' canonical order, so the bytes are those of one GPU.
+        Rank 0 returns the clip, the other ranks return None."""
         self.cfg, self.backend, self.device, self.dtype, self.family = cfg, backend, torch.device(device), dtype, family
         self.cfgp = cfg_parallel
+        self.fp = frame_parallel
+        self._shard = None
         assert cfg_parallel is None or (cfg_parallel.world == 2 and backend == "native"), "cfg_parallel needs a 2-rank heap"
+        assert frame_parallel is None or (cfg_parallel is None and backend == "native"), "frame_parallel: native, no cfg_parallel"
         self.tokenizer = load_tokenizer(model_dir, cfg.clip.vocab_size)
         with torch.device(device):
             unet, clip, vae = UNet3DConditionModel(cfg.unet), CLIPTextModel(cfg.clip), AutoencoderKLDecoder(cfg.vae)
@@ -133,7 +140,11 @@ class TextToVideoPipeline:
         return out
 
     def _run_native(self, st: dict, g: float) -> None:
-        sch, nf = st["sch"], st["nf"]
+        """``nf`` below is the number of frames THIS rank holds (all of them unless frame_parallel)."""
+        import sys
+        gemm_mod = sys.modules["arbius_b200.ops.gemm"]
+        sch, nf = st["sch"], st["nfl"]
+        P = self.fp.world if self.fp is not None else 1
         ctx = self.clip.forward(st["ids"])
         kvs = self.unet.precompute_context(ctx)
         temb = self.unet.time_projections(st["tvec"], nf)                      # [2*steps*F, sum(Cout)]
@@ -143,7 +154,11 @@ class TextToVideoPipeline:
             for b in range(2):
                 ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=sch.input_scale(i))
             if self.cfgp is None:
-                e = self.unet.forward(st["xin"], temb[2 * nf * i:2 * nf * (i + 1)], kvs)
+                gemm_mod.BATCH_SCALE = P               # every UNet GEMM's rows scale with the frames: canonical = all
+                try:
+                    e = self.unet.forward(st["xin"], temb[2 * nf * i:2 * nf * (i + 1)], kvs)
+                finally:
+                    gemm_mod.BATCH_SCALE = 1
                 ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
             else:
                 self._cfg_parallel_step(st, i, temb, kvs, g)
@@ -151,9 +166,27 @@ class TextToVideoPipeline:
                 ops.lincomb(f[dst], [(c, st["noise"][i] if s == "noise" else f[s]) for c, s in terms])
         ops.lincomb(None, [(1.0, f["x"])], dst_m=st["lat"], m_scale=1.0)
         chunks = []
-        for i in range(0, nf, st["vae_chunk"]):
-            chunks.append(ops.finalize_u8(self.vae.forward(st["lat"][0, i:i + st["vae_chunk"]])))
+        chunk = st["vae_chunk"]
+        vscale = 1
+        if P > 1 and chunk % P == 0:
+            chunk, vscale = chunk // P, P              # the single-GPU chunk, cut over the ranks
+        gemm_mod.BATCH_SCALE = vscale
+        try:
+            for i in range(0, nf, chunk):
+                chunks.append(ops.finalize_u8(self.vae.forward(st["lat"][0, i:i + chunk])))
+        finally:
+            gemm_mod.BATCH_SCALE = 1
         st["u8"] = torch.cat(chunks, 0) if len(chunks) > 1 else chunks[0]
+        if self.fp is not None:
+            # every rank stores its frames into rank 0's clip buffer, then all meet: rank 0 owns the whole clip
+            from ...parallel.frame_shard import _lib as fs_lib
+            u8 = st["u8"].contiguous()
+            nbytes = u8.numel()
+            dst = self.fp.peer_ptr(0, st["clip_off"]) + self.fp.rank * nbytes
+            ops.native.check(fs_lib().ab_peer_copy2d(dst, nbytes, u8.data_ptr(), nbytes, nbytes, 1,
+                                                     ops.native.stream_ptr()), "ab_peer_copy2d")
+            self.fp.barrier_replayable()
+            st["u8"] = st["clip"]
 
     def _cfg_parallel_step(self, st: dict, i: int, temb, kvs, g: float) -> None:
         """This rank's guidance branch of step i, exchanged through the peer heap (see SD15Pipeline._cfg_parallel_step)."""
@@ -181,23 +214,36 @@ class TextToVideoPipeline:
         dev, dt = self.device, self.dtype
         h, w = height // self.vae_scale, width // self.vae_scale
         key = (nf, steps, width, height, g, sched)
+        P = self.fp.world if self.fp is not None else 1
+        rank = self.fp.rank if self.fp is not None else 0
+        assert nf % P == 0, "frames must divide over the frame-parallel ranks"
+        nfl = nf // P
         st = self._graphs.get(key)
         if st is None:
             sch = make_scheduler(sched)
             sch.set_timesteps(steps)
             names = {"x", "eps", "tmp"} | set(sch.history)
-            shape = (1, nf, h, w, 4)
-            st = dict(sch=sch, nf=nf, ids=torch.zeros((2, self.tokenizer.max_len), dtype=torch.int64, device=dev),
+            shape = (1, nfl, h, w, 4)
+            st = dict(sch=sch, nf=nf, nfl=nfl, ids=torch.zeros((2, self.tokenizer.max_len), dtype=torch.int64, device=dev),
                       ids_host=torch.zeros((2, self.tokenizer.max_len), dtype=torch.int64).pin_memory(),
                       tvec=torch.tensor([t for t in sch.timesteps for _ in range(2)], dtype=torch.float32, device=dev),
                       noise0=torch.zeros(shape, dtype=torch.float32, device=dev),
                       noise=[torch.zeros(shape, dtype=torch.float32, device=dev) for _ in sch.timesteps] if sch.stochastic else [],
                       f32={n: torch.zeros(shape, dtype=torch.float32, device=dev) for n in names},
-                      xin=torch.zeros((2, nf, h, w, 4), dtype=dt, device=dev), lat=torch.zeros(shape, dtype=dt, device=dev),
+                      xin=torch.zeros((2, nfl, h, w, 4), dtype=dt, device=dev), lat=torch.zeros(shape, dtype=dt, device=dev),
                       out_host=torch.zeros((nf, height, width, 3), dtype=torch.uint8).pin_memory(),
                       vae_chunk=max(1, min(nf, (1 << 22) // max(1, height * width // 4))), graph=None, launches=0)
             if self.cfgp is not None:
                 st["ex"], st["ex_off"] = self.cfgp.alloc((2,) + shape, dt)
+            if self.fp is not None:
+                from ...parallel.frame_shard import FrameShard
+                ucfg = self.cfg.unet
+                max_c = max(ucfg.block_out_channels[0], self.unet.transformer_in.inner)
+                self.fp.reset()
+                self._shard = FrameShard(self.fp, 2, nfl, h * w, max_c, dt, ucfg.norm_groups)
+                self.unet.set_frame_shard(self._shard)
+                st["clip"], st["clip_off"] = self.fp.alloc((nf, height, width, 3), torch.uint8)
+                self._graphs.clear()                   # the heap was laid out anew: older states' buffers are gone
             if self.use_graph:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())
@@ -216,10 +262,11 @@ class TextToVideoPipeline:
         st["ids"].copy_(st["ids_host"], non_blocking=True)
         self.h2d_bytes = ids.numel() * 8
         lib = ops.native.load()
-        n = nf * h * w * 4
-        ops.native.check(lib.ab_philox_normal(st["noise0"].data_ptr(), n, seed, 0, 0, ops.native.stream_ptr()), "philox")
+        n = nfl * h * w * 4
+        off = rank * n                                  # global element index of this rank's first frame
+        ops.native.check(lib.ab_philox_normal(st["noise0"].data_ptr(), n, seed, 0, off, ops.native.stream_ptr()), "philox")
         for i, nb in enumerate(st["noise"]):
-            ops.native.check(lib.ab_philox_normal(nb.data_ptr(), n, seed, 1 + i, 0, ops.native.stream_ptr()), "philox")
+            ops.native.check(lib.ab_philox_normal(nb.data_ptr(), n, seed, 1 + i, off, ops.native.stream_ptr()), "philox")
         if st["graph"] is not None:
             st["graph"].replay()
             self.last_launches = st["launches"] + 1 + len(st["noise"])
@@ -227,6 +274,10 @@ class TextToVideoPipeline:
             n0 = ops.native.launch_count()
             self._run_native(st, g)
             self.last_launches = ops.native.launch_count() - n0 + 1 + len(st["noise"])
+        if rank != 0:
+            torch.cuda.current_stream().synchronize()
+            self.d2h_bytes = 0
+            return None
         st["out_host"].copy_(st["u8"], non_blocking=True)
         torch.cuda.current_stream().synchronize()
         self.d2h_bytes = st["out_host"].numel()
@@ -240,4 +291,6 @@ class TextToVideoPipeline:
                                num_frames=inp.get("num_frames"), num_inference_steps=int(inp.get("num_inference_steps", 50)),
                                width=inp.get("width"), height=inp.get("height"), guidance_scale=inp.get("guidance_scale"),
                                seed=int(inp.get("seed", 0)))
+        if frames is None:                              # a frame-parallel rank other than 0: rank 0 has the clip
+            return None
         return encode_mp4(frames, int(inp.get("fps", self.cfg.default_fps)))

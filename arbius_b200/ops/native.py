@@ -40,6 +40,7 @@ class GemmArgs(C.Structure):
         ("ldo", C.c_int),
         ("ldr", C.c_int),
         ("ldrb", C.c_int),
+        ("halo", C.c_int),
     ]
 
 

@@ -13,7 +13,7 @@ class TemporalAttnArgs(C.Structure):
     _fields_ = [("q", C.c_void_p * 8), ("k", C.c_void_p * 8), ("v", C.c_void_p * 8), ("out", C.c_void_p * 8),
                 ("nsrc", C.c_int), ("batch", C.c_int), ("heads", C.c_int), ("frames", C.c_int), ("hw", C.c_int),
                 ("head_dim", C.c_int), ("row_stride", C.c_longlong), ("out_row_stride", C.c_longlong),
-                ("scale", C.c_float), ("dtype", C.c_int)]
+                ("scale", C.c_float), ("dtype", C.c_int), ("pix_begin", C.c_int), ("pix_count", C.c_int)]
 
 
 def _lib():
@@ -27,8 +27,12 @@ def _lib():
 
 def temporal_attn_ptrs(q_ptrs: Sequence[int], k_ptrs: Sequence[int], v_ptrs: Sequence[int], out_ptrs: Sequence[int],
                        batch: int, frames: int, hw: int, heads: int, head_dim: int, row_stride: int,
-                       out_row_stride: int, dtype: torch.dtype, scale: Optional[float] = None) -> None:
+                       out_row_stride: int, dtype: torch.dtype, scale: Optional[float] = None,
+                       pix_begin: int = 0, pix_count: int = 0) -> None:
+    """Multi-source form: source s holds frames [s*F/n, (s+1)*F/n) as [B, F/n, HW, row_stride]; ``frames`` is the total.
+    ``pix_count`` > 0 restricts the launch to a pixel band (the frame-sharded UNet3D: one band per GPU)."""
     a = TemporalAttnArgs()
+    a.pix_begin, a.pix_count = pix_begin, pix_count
     n = len(q_ptrs)
     for s in range(n):
         a.q[s], a.k[s], a.v[s], a.out[s] = q_ptrs[s], k_ptrs[s], v_ptrs[s], out_ptrs[s]

@@ -274,13 +274,22 @@ def main() -> int:
         # latency, byte-identical output). world/2 tasks are in flight at a time.
         from arbius_b200.parallel.groups import subset_group
         from arbius_b200.parallel.symm import PeerHeap
-        heap = PeerHeap(64 << 20, group=subset_group(2))
-        if video:
+        frame_par = video and world in (2, 4, 8) and vcfg.default_frames % world == 0
+        if frame_par:
+            # text-to-video: ONE task over all the GPUs, frames sharded (parallel/frame_shard.py)
+            del pipe
+            torch.cuda.empty_cache()
+            heap = PeerHeap((3 << 30) if args.model != "video-tiny" else (256 << 20))
+            lpipe = TextToVideoPipeline(vcfg, backend="native", device=f"cuda:{local}", dtype=dt, family=args.model,
+                                        frame_parallel=heap)
+        elif video:
+            heap = PeerHeap(64 << 20, group=subset_group(2))
             lpipe = TextToVideoPipeline(vcfg, backend="native", device=f"cuda:{local}", dtype=dt, family=args.model,
                                         cfg_parallel=heap)
         else:
+            heap = PeerHeap(64 << 20, group=subset_group(2))
             lpipe = SD15Pipeline(cfg, backend="native", device=f"cuda:{local}", dtype=dt, seed=0, cfg_parallel=heap)
-        pair = rank // 2
+        pair = 0 if frame_par else rank // 2
         for i in range(W):
             lpipe.generate(seed=5000 + pair * 100 + i, **base)
         barrier()
@@ -291,9 +300,12 @@ def main() -> int:
         l1.record()
         barrier()
         lat_ms_pair = reduce_max(l0.elapsed_time(l1)) / K
-        out["latency_mode"] = {"parallelism": f"guidance-parallel pairs x task-dp{world // 2}", "ms_per_task": round(lat_ms_pair, 3),
-                               "tasks_per_hour": round((world // 2) / (lat_ms_pair / 1e3) * 3600.0, 2),
-                               "bytes": "identical to the single-GPU pipeline (tests/mp_cfg_parallel.py)"}
+        inflight = 1 if frame_par else world // 2
+        out["latency_mode"] = {"parallelism": f"frame-parallel sp{world}" if frame_par else f"guidance-parallel pairs x task-dp{world // 2}",
+                               "ms_per_task": round(lat_ms_pair, 3),
+                               "tasks_per_hour": round(inflight / (lat_ms_pair / 1e3) * 3600.0, 2),
+                               "bytes": "identical to the single-GPU pipeline (tests/mp_frame_parallel.py)" if frame_par
+                               else "identical to the single-GPU pipeline (tests/mp_cfg_parallel.py)"}
         heap.close()
     if rank == 0:
         print(json.dumps(out))

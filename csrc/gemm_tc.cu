@@ -40,7 +40,7 @@ struct GemmParams {
     int M, N, Nout;
     int k1_chunks, k2_chunks;   // 64-wide chunks from source 1 / source 2 (per tap in conv mode)
     int taps;                   // 1 (linear) or 9 (conv)
-    int conv, nimg, H, W;
+    int conv, nimg, H, W, halo;
     int bw_log2, bh_log2;       // conv tile: BW x BH x BI pixels, all powers of two, product 128
     int tiles_w, tiles_h;
     int rows_per_group;
@@ -262,7 +262,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         // conv == 1: 3x3 taps; conv == 2: 3x1 taps along H only (temporal Conv3d (3,1,1) on [B, F, HW, C])
                         const int dh = p.conv == 2 ? tap - 1 : tap / 3 - 1;
                         const int dw = p.conv == 2 ? 0 : tap % 3 - 1;
-                        tma_load_4d(sas, ma, &full_bar[stage], c0, w0s[s] + dw, h0s[s] + dh, i0s[s]);
+                        tma_load_4d(sas, ma, &full_bar[stage], c0, w0s[s] + dw, h0s[s] + dh + p.halo, i0s[s]);
                     } else {
                         if (p.nsrc > 1) {
                             const int src = tile_ms[s] / p.tiles_per_src;
@@ -638,7 +638,8 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     p.taps = a->conv == 2 ? 3 : (a->conv ? 9 : 1);
     p.k1_chunks = (a->K2 > 0 || a->conv) ? a->K1 / BK : (a->K1 + BK - 1) / BK;
     p.k2_chunks = a->K2 > 0 ? (a->conv ? a->K2 / BK : (a->K2 + BK - 1) / BK) : 0;
-    p.conv = a->conv; p.nimg = a->nimg; p.H = a->H; p.W = a->W;
+    p.conv = a->conv; p.nimg = a->nimg; p.H = a->H; p.W = a->W; p.halo = a->halo;
+    AB_REQUIRE(a->halo == 0 || (a->halo == 1 && a->conv == 2 && a->K2 == 0), "halo rows: temporal conv (conv == 2) without virtual concat only");
     p.rows_per_group = a->conv ? a->H * a->W : a->rows_per_group;
     p.act = a->act; p.geglu = a->geglu;
     p.out_scale = a->out_scale == 0.f ? 1.f : a->out_scale;
@@ -706,8 +707,9 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     CUtensorMap tmA, tmA2, tmB;
     const int esz = 2;
     if (a->conv) {
-        uint64_t dims[4] = {(uint64_t)a->K1, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
-        uint64_t str[3] = {(uint64_t)a->K1 * esz, (uint64_t)a->W * a->K1 * esz, (uint64_t)a->H * a->W * a->K1 * esz};
+        const uint64_t Hin = (uint64_t)a->H + 2 * (uint64_t)a->halo;   // halo rows are real data, not the zero fill
+        uint64_t dims[4] = {(uint64_t)a->K1, (uint64_t)a->W, Hin, (uint64_t)a->nimg};
+        uint64_t str[3] = {(uint64_t)a->K1 * esz, (uint64_t)a->W * a->K1 * esz, Hin * a->W * a->K1 * esz};
         uint32_t box[4] = {BK, (uint32_t)ct.bw, (uint32_t)ct.bh, (uint32_t)ct.bi};
         if (ab_make_tensor_map(&tmA, a->dtype, 4, a->a, dims, str, box, 128)) return -1;
         tmA2 = tmA;

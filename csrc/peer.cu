@@ -103,3 +103,35 @@ extern "C" int ab_peer_barrier(void* const* flag_ptrs, int rank, int world, unsi
     ab_count_launch(1);
     return 0;
 }
+
+// ---- strided copy between this GPU's memory and a peer's (halo rows of a sharded tensor) ------------------------
+// rows x width_bytes, 16 bytes per thread and access; src or dst may be a peer-mapped address. src == nullptr writes
+// zeros (the sequence ends, where the conv's padding is zero). Plain loads/stores: graph-capturable, stream-ordered.
+namespace ab {
+__global__ void __launch_bounds__(256) peer_copy2d_kernel(uint4* __restrict__ dst, long long dst_pitch16,
+                                                          const uint4* __restrict__ src, long long src_pitch16,
+                                                          long long width16, int rows) {
+    const long long total = width16 * rows;
+    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
+        const long long r = i / width16, c = i - r * width16;
+        dst[r * dst_pitch16 + c] = src ? src[r * src_pitch16 + c] : make_uint4(0, 0, 0, 0);
+    }
+}
+}  // namespace ab
+
+extern "C" int ab_peer_copy2d(void* dst, long long dst_pitch, const void* src, long long src_pitch, long long width_bytes,
+                              int rows, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(dst && rows > 0 && width_bytes > 0, "bad arguments");
+    AB_REQUIRE(width_bytes % 16 == 0 && dst_pitch % 16 == 0 && src_pitch % 16 == 0 &&
+               (reinterpret_cast<uintptr_t>(dst) & 15) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0,
+               "16-byte alignment required");
+    const long long total = width_bytes / 16 * rows;
+    const int blocks = static_cast<int>(total / 256 + 1 < 148 * 8 ? total / 256 + 1 : 148 * 8);
+    ab::peer_copy2d_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<uint4*>(dst), dst_pitch / 16,
+                                                       reinterpret_cast<const uint4*>(src), src_pitch / 16,
+                                                       width_bytes / 16, rows);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

@@ -34,7 +34,7 @@ __device__ __forceinline__ float ex2_approx_ta(float x) {
 
 struct TaParams {
     void* out[8];            // per-source output buffers [B, F_s, HW, heads*D] (row stride o_ls elements)
-    int batch, heads, frames, frames_per_src, nsrc, hw, px, head_dim;
+    int batch, heads, frames, frames_per_src, nsrc, hw, px, head_dim, pix_begin, pix_end;
     long long o_ls;
     float scale_log2;
 };
@@ -62,7 +62,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int pix0 = blockIdx.x * p.px;
+    const int pix0 = p.pix_begin + blockIdx.x * p.px;
     const int h = blockIdx.y;
     const int b = blockIdx.z;
     const int D = p.head_dim;
@@ -179,7 +179,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
         const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
         const int f = PM ? r % p.frames : r / p.px;
         const int pix = pix0 + my_pix;
-        const bool ok = r < R && pix < p.hw;
+        const bool ok = r < R && pix < p.pix_end;
         const int src = ok ? f / p.frames_per_src : 0;
         const int fl = f - src * p.frames_per_src;
         T* orow = reinterpret_cast<T*>(p.out[src]) +
@@ -226,7 +226,13 @@ extern "C" int ab_temporal_attn(const ab_temporal_attn_args* a, void* stream_) {
     p.head_dim = D; p.o_ls = a->out_row_stride;
     const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
     p.scale_log2 = scale * 1.4426950408889634f;
-    const bool pm = (Fs % 8 == 0);
+    // Pixel-major needs every pixel's block of F rows to start on a 1024-byte swizzle atom (F % 8 == 0); a source's
+    // F_s rows inside that block only need the 128-byte row alignment: TMA swizzles by shared-memory address.
+    const bool pm = (F % 8 == 0);
+    const int pix_begin = a->pix_count > 0 ? a->pix_begin : 0;
+    const int pix_count = a->pix_count > 0 ? a->pix_count : a->hw;
+    AB_REQUIRE(pix_begin >= 0 && pix_begin + pix_count <= a->hw, "pixel band outside the frame");
+    p.pix_begin = pix_begin; p.pix_end = pix_begin + pix_count;
     TaMaps maps;
     for (int s = 0; s < nsrc; ++s) {
         AB_REQUIRE(a->q[s] && a->k[s] && a->v[s] && a->out[s], "null source pointer");
@@ -241,7 +247,7 @@ extern "C" int ab_temporal_attn(const ab_temporal_attn_args* a, void* stream_) {
     }
     for (int s = nsrc; s < 8; ++s) { maps.q[s] = maps.q[0]; maps.k[s] = maps.k[0]; maps.v[s] = maps.v[0]; }
     constexpr int smem = 3 * TA_TILE_BYTES + 8 * 8 + 16 + 1024;
-    dim3 grid((a->hw + px - 1) / px, a->heads, a->batch);
+    dim3 grid((pix_count + px - 1) / px, a->heads, a->batch);
 #define AB_TA_LAUNCH(T, PMV)                                                                                      \
     do {                                                                                                         \
         if (ab_ensure_max_smem(reinterpret_cast<const void*>(temporal_attn_kernel<T, PMV>), smem)) return -1;    \

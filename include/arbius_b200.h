@@ -64,6 +64,9 @@ typedef struct {
   int ldo;                  /* output row stride in elements, 0 = Nout */
   int ldr;                  /* residual row stride in elements, 0 = Nout */
   int ldrb;                 /* rowbias row stride in elements, 0 = N */
+  int halo;                 /* conv == 2 only: A holds `halo` extra rows of H before and after every image
+                             * ([nimg, H + 2*halo, W, K1], H counts output rows): a frame-sharded temporal conv whose
+                             * neighbour frames were copied in from the GPUs next door. 0 or 1. */
 } ab_gemm_args;
 int ab_gemm(const ab_gemm_args* args, void* stream);
 /* Multi-GPU forms of the same kernel (one NVSwitch box; pointers may be peer-mapped addresses).
@@ -108,6 +111,15 @@ typedef struct {
 } ab_groupnorm_args;
 int ab_groupnorm(const ab_groupnorm_args* args, void* stream);
 size_t ab_groupnorm_partials_bytes(int n, int groups);
+/* One sample's rows spread over world = 2, 4 or 8 GPUs (rank r holds canonical shards [r*8/world, (r+1)*8/world)):
+ * stats writes this GPU's partial moments into peer-visible memory ([n][8][sub][groups] x 16 B; see
+ * ab_groupnorm_partials_bytes for an upper bound), the GPUs meet at a barrier, apply merges all partials in canonical
+ * order (part_srcs[r] = rank r's array, r < world) and normalises the local rows. args->hw is the local row count;
+ * args->partials the usual local workspace; y_batch_stride (elements, 0 = hw*C) lets y be the interior of a padded
+ * buffer. Output bytes equal ab_groupnorm on the undivided tensor. */
+int ab_groupnorm_sharded_stats(const ab_groupnorm_args* args, int world, int rank, void* partials_out, void* stream);
+int ab_groupnorm_sharded_apply(const ab_groupnorm_args* args, int world, void* const* part_srcs, long long y_batch_stride,
+                               void* stream);
 /* Same operation as ab_groupnorm for callers that cannot allocate device memory (a host whose arena
  * already owns all of HBM, a plain C caller with no allocator, a loop that cannot take the device-wide
  * sync of cudaMalloc). args->partials is ignored: the statistics scratch is a ~0.5 MB array compiled
@@ -175,6 +187,9 @@ typedef struct {
   long long out_row_stride;
   float scale;              /* 0 = 1/sqrt(head_dim) */
   int dtype;
+  int pix_begin, pix_count; /* this launch handles pixels [pix_begin, pix_begin + pix_count) of hw (0, 0 = all): with
+                             * frames sharded over GPUs, every GPU takes a pixel band, reads that band's Q/K/V frames
+                             * from all sources and stores each frame's output to the GPU that owns the frame */
 } ab_temporal_attn_args;
 int ab_temporal_attn(const ab_temporal_attn_args* args, void* stream);
 
@@ -187,6 +202,9 @@ int ab_ipc_close_handle(void* ptr);
 int ab_peer_barrier(void* const* flag_ptrs, int rank, int world, unsigned int epoch, void* stream);
 /* same barrier with the epoch kept in device memory (own flag words), so it can be captured in a CUDA graph and replayed */
 int ab_peer_barrier_auto(void* const* flag_ptrs, int rank, int world, void* stream);
+/* rows x width_bytes strided copy (16-byte units); src or dst may be a peer-mapped address, src == NULL writes zeros */
+int ab_peer_copy2d(void* dst, long long dst_pitch, const void* src, long long src_pitch, long long width_bytes,
+                   int rows, void* stream);
 
 /* ---- K12/K15/G1/G3/S11: elementwise ------------------------------------------------------------- */
 /* counter-based N(0,1): out[i] = normal(philox4x32-10(seed, stream_id, offset + i)); i is the GLOBAL
