@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "zeroscopev2xl", "damo", "kandinsky2"])
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--task-batch", type=int, default=1, help="anythingv3: independent tasks per forward")
     ap.add_argument("--out", default="gpurun_out/profile_task.json")
     a = ap.parse_args()
     if a.model == "anythingv3":
@@ -38,11 +39,16 @@ def main():
         cfg.steps = a.steps
         pipe = Kandinsky2Pipeline(cfg, backend=a.impl, device="cuda", dtype=torch.float16, use_graph=False)
         kw = dict(prompt="arbius test cat", width=768, height=768)
-    pipe.generate(seed=1, **kw)
+    def run(seed):
+        if a.task_batch > 1 and a.model == "anythingv3":
+            pipe.generate_batch([dict(kw, seed=seed + i) for i in range(a.task_batch)])
+        else:
+            pipe.generate(seed=seed, **kw)
+    run(1)
     torch.cuda.synchronize()
     from torch.profiler import ProfilerActivity, profile
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
-        pipe.generate(seed=2, **kw)
+        run(10)
         torch.cuda.synchronize()
     agg = defaultdict(lambda: [0.0, 0])
     for ev in prof.events():
