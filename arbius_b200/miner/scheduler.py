@@ -40,11 +40,19 @@ class CostModel:
     MEASURED_B200 = {"anythingv3": {1: 127.0, 2: 110.0}, "zeroscopev2xl": {1: 15000.0, 2: 7800.0},
                      "kandinsky2": {1: 972.0}}
 
+    # ms per task of the frame-parallel text-to-video predictors (tests/mp_frame_parallel.py scaled to 50 steps)
+    MEASURED_B200_FRAMES = {}                           # filled from profiles/multigpu_frame_parallel_v0.md
+
     @classmethod
-    def measured_b200(cls, pair_families: Sequence[str] = ()) -> "CostModel":
+    def measured_b200(cls, pair_families: Sequence[str] = (), frame_families: Sequence[str] = (),
+                      frame_sizes: Sequence[int] = ()) -> "CostModel":
         table = {}
         for fam, row in cls.MEASURED_B200.items():
             table[fam] = {p: ms for p, ms in row.items() if p == 1 or fam in pair_families}
+        for fam in frame_families:
+            for p, ms in cls.MEASURED_B200_FRAMES.get(fam, {}).items():
+                if p in frame_sizes:
+                    table.setdefault(fam, {})[p] = ms
         return cls(table=table)
 
     def ms(self, family: str, p: int) -> float:

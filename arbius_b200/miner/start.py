@@ -106,7 +106,27 @@ def start(config_path: str, run: bool = True) -> MinerNode:
                                                                                 tiny=bool(ent.get("tiny")))
                                                for g in range(0, gpus - 1, 2)}
                     pair_families.append(m.name)
-        cost = CostModel.measured_b200(pair_families)
+        # ``ml.native.frame_parallel: [2, 4, 8]`` (or true = the whole box): text-to-video tasks may be spread over
+        # aligned GPU subsets of those sizes, frames sharded (models/registry.py build_frame_parallel_predictor)
+        fp_sizes = c.ml.native.get("frame_parallel") or []
+        if fp_sizes is True:
+            fp_sizes = [gpus]
+        frame_families = []
+        for m in models:
+            from ..models.registry import FRAME_FAMILIES, build_frame_parallel_predictor
+            if m.name not in FRAME_FAMILIES:
+                continue
+            ent = c.ml.native.get("models", {}).get(m.id, {})
+            for p in sorted(int(x) for x in fp_sizes):
+                if p not in (2, 4, 8) or p > gpus:
+                    continue
+                for g in range(0, gpus - p + 1, p):
+                    devs = tuple(range(g, g + p))
+                    subset_predictors.setdefault(m.id, {})[devs] = build_frame_parallel_predictor(
+                        m.name, devices=devs, model_dir=ent.get("weights"), tiny=bool(ent.get("tiny")))
+                if m.name not in frame_families:
+                    frame_families.append(m.name)
+        cost = CostModel.measured_b200(pair_families, frame_families, [int(x) for x in fp_sizes])
     ml = make_backend(c, predictors, subset_predictors, slots)
     n_gpus = c.scheduler.gpus or max([ml.endpoints(m) for m in models] + [1])
     n_gpus = max(p for p in (1, 2, 4, 8) if p <= n_gpus)

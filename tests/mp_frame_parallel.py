@@ -69,6 +69,12 @@ def main():
         if rank == 0:
             print(f"RESULT zeroscope frame_parallel world={world} 4-step latency_ms={t_par:.1f} single_gpu_latency_ms={t_ref:.1f} "
                   f"barriers_per_task={zpar._shard.barriers // 2}", flush=True)
+        if os.environ.get("AB_FP_STEPS50", "0") == "1":        # the template's default task: 50 steps
+            zkw["num_inference_steps"] = 50
+            zpar.generate(seed=5, **zkw)                       # capture
+            t50 = vtime(zpar)
+            if rank == 0:
+                print(f"RESULT zeroscope frame_parallel world={world} 50-step task latency_ms={t50:.1f}", flush=True)
     heap.close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
