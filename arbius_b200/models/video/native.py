@@ -41,7 +41,8 @@ class _TemporalConv:
             for i, (nw, nb, cw, cb) in enumerate(self.stages):
                 pad = self.shard.groupnorm(y, nw, nb, self.groups, 1e-5, "silu", padded_parity=i & 1)
                 self.shard.exchange_halos(pad, i & 1)
-                y = ops.conv_temporal(pad, cw, cb, residual=idt if i == 3 else None, halo=True)
+                y = ops.conv_temporal(pad, cw, cb, residual=idt if i == 3 else None, halo=True,
+                                      frame_ranks=self.shard.world)
             return y.view(b, f, h, w, c)
         for i, (nw, nb, cw, cb) in enumerate(self.stages):
             y = ops.groupnorm(y, nw, nb, self.groups, 1e-5, "silu")           # stats over (F, H, W) per sample

@@ -65,7 +65,8 @@ class TextToVideoPipeline:
         self.fp = frame_parallel
         self._shard = None
         assert cfg_parallel is None or (cfg_parallel.world == 2 and backend == "native"), "cfg_parallel needs a 2-rank heap"
-        assert frame_parallel is None or (cfg_parallel is None and backend == "native"), "frame_parallel: native, no cfg_parallel"
+        assert frame_parallel is None or backend == "native", "frame_parallel needs the native backend"
+        # both may be given (two heaps over different rank groups): guidance branch x frame shard, 2*P ranks per task
         self.tokenizer = load_tokenizer(model_dir, cfg.clip.vocab_size)
         with torch.device(device):
             unet, clip, vae = UNet3DConditionModel(cfg.unet), CLIPTextModel(cfg.clip), AutoencoderKLDecoder(cfg.vae)
@@ -191,9 +192,9 @@ class TextToVideoPipeline:
     def _cfg_parallel_step(self, st: dict, i: int, temb, kvs, g: float) -> None:
         """This rank's guidance branch of step i, exchanged through the peer heap (see SD15Pipeline._cfg_parallel_step)."""
         import sys
-        heap, r, par, nf = self.cfgp, self.cfgp.rank, i & 1, st["nf"]
+        heap, r, par, nf = self.cfgp, self.cfgp.rank, i & 1, st["nfl"]
         gemm_mod = sys.modules["arbius_b200.ops.gemm"]
-        gemm_mod.BATCH_SCALE = 2
+        gemm_mod.BATCH_SCALE = 2 * (self.fp.world if self.fp is not None else 1)
         try:
             rows = temb[2 * nf * i + r * nf:2 * nf * i + (r + 1) * nf]
             e = self.unet.forward(st["xin"][r:r + 1], rows, [kv[r:r + 1] for kv in kvs])
@@ -240,7 +241,7 @@ class TextToVideoPipeline:
                 ucfg = self.cfg.unet
                 max_c = max(ucfg.block_out_channels[0], self.unet.transformer_in.inner)
                 self.fp.reset()
-                self._shard = FrameShard(self.fp, 2, nfl, h * w, max_c, dt, ucfg.norm_groups)
+                self._shard = FrameShard(self.fp, 2 if self.cfgp is None else 1, nfl, h * w, max_c, dt, ucfg.norm_groups)
                 self.unet.set_frame_shard(self._shard)
                 st["clip"], st["clip_off"] = self.fp.alloc((nf, height, width, 3), torch.uint8)
                 self._graphs.clear()                   # the heap was laid out anew: older states' buffers are gone

@@ -195,11 +195,12 @@ def pack_temporal_conv_weight(w: torch.Tensor) -> torch.Tensor:
 
 def conv_temporal(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
                   residual: Optional[torch.Tensor] = None, act: Optional[str] = None, splitk: int = 0,
-                  block_n: int = 0, halo: bool = False) -> torch.Tensor:
+                  block_n: int = 0, halo: bool = False, frame_ranks: int = 0) -> torch.Tensor:
     """Temporal Conv3d (3,1,1), pad (1,0,0), on channels-last video x [B, F, HW, C] -> [B, F, HW, Cout].
     Same implicit-GEMM kernel as conv3x3 with a 3x1 tap pattern over the (F, HW) "image".
     ``halo``: x is [B, F + 2, HW, C] — the local frames of a frame-sharded clip with the neighbours' frames (or zeros at
-    the clip's ends) in rows 0 and F+1; ``BATCH_SCALE`` then counts the ranks the frames are spread over."""
+    the clip's ends) in rows 0 and F+1; ``frame_ranks`` is the number of ranks the frames are spread over
+    (default: ``BATCH_SCALE``, which may also carry a guidance-branch split of the batch)."""
     lib = native.load()
     b, f, hw, c = x.shape
     if halo:
@@ -215,7 +216,11 @@ def conv_temporal(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.
     a.halo = 1 if halo else 0
     a.act, a.out_scale = ACT[act], 1.0
     a.dtype = native.dtype_code(x.dtype)
-    key = f"tconv:{b}x{_canon(f)}x{hw}:{n}:{c}" if halo else f"tconv:{_canon(b)}x{f}x{hw}:{n}:{c}"
+    if halo:
+        fr = frame_ranks or int(BATCH_SCALE)
+        key = f"tconv:{_canon(b) // fr}x{f * fr}x{hw}:{n}:{c}"
+    else:
+        key = f"tconv:{_canon(b)}x{f}x{hw}:{n}:{c}"
     if RECORD is not None:
         RECORD.append(key)
     cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None

@@ -52,3 +52,18 @@ def subset_group(size: int):
 def subset_ranks(rank: int, size: int) -> List[int]:
     start = rank // size * size
     return list(range(start, start + size))
+
+
+_strided_cache = {}
+
+
+def strided_group(stride: int):
+    """The ranks congruent to this one modulo ``stride`` (e.g. stride 2: the ranks that run the same guidance branch when
+    aligned pairs split the branches — the frame-parallel group of a guidance x frame layout). Collective, like
+    ``subset_group``."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    if world == 1 or stride <= 1:
+        return None
+    if stride not in _strided_cache:
+        _strided_cache[stride] = [dist.new_group(list(range(r, world, stride))) for r in range(stride)]
+    return _strided_cache[stride][dist.get_rank() % stride]

@@ -19,11 +19,22 @@ def main():
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
     full = os.environ.get("AB_FP_FULL", "0") == "1"
-    heap = PeerHeap((3 << 30) if full else (256 << 20))
+    # AB_FP_CFG=1: guidance x frame layout — aligned pairs split the two guidance branches, the ranks of equal parity
+    # share the frames (world 4: 2 x 2, world 8: 2 x 4)
+    both = os.environ.get("AB_FP_CFG", "0") == "1"
+    extra = {}
+    if both:
+        from arbius_b200.parallel.groups import strided_group, subset_group
+        assert world in (4, 8)
+        extra["cfg_parallel"] = PeerHeap(64 << 20, group=subset_group(2))
+        heap = PeerHeap((3 << 30) if full else (256 << 20), group=strided_group(2))
+    else:
+        heap = PeerHeap((3 << 30) if full else (256 << 20))
+    layout = f"cfg2 x sp{world // 2}" if both else f"sp{world}"
     ok = True
     cfg = TextToVideoConfig.tiny()
     ref = TextToVideoPipeline(cfg, backend="native", device=dev, dtype=torch.float16, family="video-tiny")
-    par = TextToVideoPipeline(cfg, backend="native", device=dev, dtype=torch.float16, family="video-tiny", frame_parallel=heap)
+    par = TextToVideoPipeline(cfg, backend="native", device=dev, dtype=torch.float16, family="video-tiny", frame_parallel=heap, **extra)
     for sched in ("DDIM", "K_EULER_ANCESTRAL"):
         kw = dict(prompt="a panda eating bamboo", negative_prompt="noisy", num_inference_steps=3, width=64, height=64,
                   num_frames=8, scheduler=sched)
@@ -37,8 +48,8 @@ def main():
                 bad = (a != b1).reshape(a.shape[0], -1).any(1)
                 print(f"frames that differ: {bad.nonzero()[0].tolist()} max diff {int(abs(a.astype(int) - b1.astype(int)).max())}", flush=True)
         else:
-            same = b1 is None and b2 is None
-        print(f"rank {rank} video-tiny {sched} world={world} bit-identical={same}", flush=True)
+            same = (b1 is None and b2 is None) or both
+        print(f"rank {rank} video-tiny {sched} world={world} {layout} bit-identical={same}", flush=True)
         ok = ok and same
     if full:
         del ref, par
@@ -60,22 +71,24 @@ def main():
         t_ref = vtime(zref)
         del zref
         torch.cuda.empty_cache()
-        zpar = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16, frame_parallel=heap)
+        zpar = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16, frame_parallel=heap, **extra)
         b = zpar.generate(seed=3, **zkw)
-        same = bool((a == b).all()) if rank == 0 else b is None
-        print(f"rank {rank} ZeroScope XL 1024x576x24 (4 steps) world={world} bit-identical={same}", flush=True)
+        same = bool((a == b).all()) if rank == 0 else (b is None or both)
+        print(f"rank {rank} ZeroScope XL 1024x576x24 (4 steps) world={world} {layout} bit-identical={same}", flush=True)
         ok = ok and same
         t_par = vtime(zpar)
         if rank == 0:
-            print(f"RESULT zeroscope frame_parallel world={world} 4-step latency_ms={t_par:.1f} single_gpu_latency_ms={t_ref:.1f} "
+            print(f"RESULT zeroscope frame_parallel world={world} {layout} 4-step latency_ms={t_par:.1f} single_gpu_latency_ms={t_ref:.1f} "
                   f"barriers_per_task={zpar._shard.barriers // 2}", flush=True)
         if os.environ.get("AB_FP_STEPS50", "0") == "1":        # the template's default task: 50 steps
             zkw["num_inference_steps"] = 50
             zpar.generate(seed=5, **zkw)                       # capture
             t50 = vtime(zpar)
             if rank == 0:
-                print(f"RESULT zeroscope frame_parallel world={world} 50-step task latency_ms={t50:.1f}", flush=True)
+                print(f"RESULT zeroscope frame_parallel world={world} {layout} 50-step task latency_ms={t50:.1f}", flush=True)
     heap.close()
+    if both:
+        extra["cfg_parallel"].close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 
