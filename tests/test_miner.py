@@ -378,3 +378,17 @@ def test_task_slots_let_a_batching_predictor_merge_solves():
         t.join(10)
     assert sorted(FakePipe.groups) == [[7], [8]]
     bp.close()
+
+
+def test_cost_table_widens_video_tasks_over_idle_gpus():
+    cost = CostModel.measured_b200([], ["zeroscopev2xl"], [2, 4, 8])
+    assert cost.best_latency_p("zeroscopev2xl", 8) == 8 and cost.best_latency_p("zeroscopev2xl", 4) == 4
+    assert cost.best_throughput_p("zeroscopev2xl", 8) == 1               # 8 GPUs on one clip never beat 8 clips at once
+    pl = SubsetPlanner(8)
+    assert pl.choose_p("zeroscopev2xl", 1, cost, "latency") == 8          # a lone clip takes the box
+    assert pl.choose_p("zeroscopev2xl", 2, cost, "latency") == 4          # two clips: half each
+    assert pl.choose_p("zeroscopev2xl", 8, cost, "throughput") == 1
+    # sizes that were not built stay out of the table
+    assert CostModel.measured_b200([], ["zeroscopev2xl"], [2]).best_latency_p("zeroscopev2xl", 8) == 2
+    sim = simulate([(0.0, "zeroscopev2xl")], 8, cost, "latency")
+    assert abs(sim["p50_latency_s"] - 2.768) < 1e-6
