@@ -42,7 +42,12 @@ def handle(db: MinerDB, method: str, path: str, body: dict, node=None):
             lat = sorted(s["total_ms"] for s in node.solved)
             lines.append(f"arbius_tasks_solved_total {len(lat)}")
             if lat:
+                from ..utils import LatencyHistogram
                 lines.append(f"arbius_task_latency_ms_p50 {lat[len(lat) // 2]:.3f}")
+                hist = LatencyHistogram()
+                for ms in lat:
+                    hist.observe(ms)
+                lines.append(hist.prometheus("arbius_task_latency_ms"))
             lines.append(f"arbius_gpu_tasks_inflight {node.pool.inflight}")
         return 200, "\n".join(lines) + "\n", "text/plain"
     if method != "POST":
