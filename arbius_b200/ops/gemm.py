@@ -37,6 +37,24 @@ def _canon(m: int) -> int:
     return int(m * BATCH_SCALE)
 
 
+def _tuned_pair(key: str, actual_key: str):
+    """(block_n, splitk) for a call: split-K — the only choice that changes the summation order — always comes from the
+    canonical shape's entry; the tile width is free, so a batch of several tasks takes the entry of its real shape if
+    there is one and otherwise lets the library size the tile for the rows it really has (block_n 0)."""
+    cfg = tuned_config(key)
+    if cfg is None or BATCH_SCALE >= 1 or key == actual_key or _BATCH_BN == "canon":
+        return cfg
+    own = tuned_config(actual_key)
+    if own is None and _BATCH_BN == "small" and cfg[0] > 96:
+        return cfg                                      # wide tiles were not chosen for want of rows: keep them
+    return (own[0] if own is not None else 0, cfg[1])
+
+
+import os as _os
+
+_BATCH_BN = _os.environ.get("AB_BATCH_BN", "auto")
+
+
 def tuned_config(key: str):
     global _tuned
     if _tuned is None:
@@ -123,10 +141,11 @@ def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
     a.ldr = res.stride(0) if res is not None else 0
     a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = (k1 + k2 + 63) // 64
-    key = f"{'geglu' if geglu else 'lin'}:{_canon(m)}:{n}:{k1 + k2}"
+    kind = 'geglu' if geglu else 'lin'
+    key = f"{kind}:{_canon(m)}:{n}:{k1 + k2}"
     if RECORD is not None:
         RECORD.append(key)
-    cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
+    cfg = _tuned_pair(key, f"{kind}:{m}:{n}:{k1 + k2}") if (splitk == 0 and block_n == 0) else None
     if cfg is not None:
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:
@@ -162,7 +181,7 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     key = f"conv:{_canon(b)}x{h}x{wd}:{n}:{c1 + c2}"
     if RECORD is not None:
         RECORD.append(key)
-    cfg = tuned_config(key) if (splitk == 0 and block_n == 0) else None
+    cfg = _tuned_pair(key, f"conv:{b}x{h}x{wd}:{n}:{c1 + c2}") if (splitk == 0 and block_n == 0) else None
     if cfg is not None:
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:

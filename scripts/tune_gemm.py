@@ -44,7 +44,7 @@ def time_graph(fn, iters=5):
     return best * 1e3 / REPS   # us per call
 
 
-def bench_key(key, dt=torch.float16):
+def bench_key(key, dt=torch.float16, only_splitk=None):
     parts = key.split(":")
     kind = parts[0]
     res = {}
@@ -62,8 +62,8 @@ def bench_key(key, dt=torch.float16):
                 continue
             if bn > 64 and bn >= 2 * n:
                 continue
-            for sk in SPLITS:
-                if sk > 1 and (kc // sk < 4 or m * n * sk * 4 > (512 << 20)):
+            for sk in ([only_splitk] if only_splitk else SPLITS):
+                if only_splitk is None and sk > 1 and (kc // sk < 4 or m * n * sk * 4 > (512 << 20)):
                     continue
                 def fn():
                     for i in range(REPS):
@@ -86,8 +86,8 @@ def bench_key(key, dt=torch.float16):
         for bn in BNS:
             if bn > 64 and bn >= 2 * n:
                 continue
-            for sk in SPLITS:
-                if sk > 1 and (kc // sk < 4 or m * n * sk * 4 > (512 << 20)):
+            for sk in ([only_splitk] if only_splitk else SPLITS):
+                if only_splitk is None and sk > 1 and (kc // sk < 4 or m * n * sk * 4 > (512 << 20)):
                     continue
                 def fn():
                     for i in range(REPS):
@@ -99,12 +99,43 @@ def bench_key(key, dt=torch.float16):
     return res, flops, wbytes
 
 
+def tune_batched(a):
+    """For every tuned canonical shape: the same op with task_batch x the rows, split-K fixed, best block_n."""
+    canon = json.load(open("arbius_b200/ops/tuned_sm100.json"))
+    out = {}
+    for key, (bn0, sk) in sorted(canon.items()):
+        parts = key.split(":")
+        if parts[0] == "conv":
+            b_, h, w = (int(v) for v in parts[1].split("x"))
+            if b_ != 2:
+                continue                                   # only the UNet's shapes (batch 2) grow with the task batch
+            big = f"conv:{b_ * a.task_batch}x{h}x{w}:{parts[2]}:{parts[3]}"
+        elif parts[0] in ("lin", "geglu"):
+            big = f"{parts[0]}:{int(parts[1]) * a.task_batch}:{parts[2]}:{parts[3]}"
+        else:
+            continue
+        if big in canon:
+            continue
+        res, flops, _ = bench_key(big, only_splitk=sk)
+        (bn, _), us = min(res.items(), key=lambda kv: kv[1])
+        base = res.get((bn0, sk), float("nan"))
+        out[big] = [bn, sk]
+        print(json.dumps(dict(key=big, canonical=[bn0, sk], best_bn=bn, us=round(us, 2), canonical_bn_us=round(base, 2),
+                              tflops=round(flops / us / 1e6, 1))), flush=True)
+    json.dump(out, open(a.out.replace(".json", f"_tb{a.task_batch}.json"), "w"), indent=0, sort_keys=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--write", action="store_true")
     ap.add_argument("--out", default="gpurun_out/tune_report.json")
     ap.add_argument("--size", type=int, default=512)
+    ap.add_argument("--task-batch", type=int, default=0,
+                    help="tune the tile width (only) of every recorded shape at this many tasks per batch; split-K stays "
+                         "the canonical entry's, so the bytes per task do not change")
     a = ap.parse_args()
+    if a.task_batch > 1:
+        return tune_batched(a)
     from arbius_b200.models.sd15.pipeline import SD15Config, SD15Pipeline
     pipe = SD15Pipeline(SD15Config(), backend="native", device="cuda", dtype=torch.float16, use_graph=False)
     G.RECORD = []
