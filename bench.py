@@ -242,6 +242,7 @@ def main() -> int:
     e2e_s = reduce_max(time.perf_counter() - t0)
     barrier()
 
+    e2e_group = TB if (TB > 1 and K % TB == 0) else 1      # tasks behind the last replay's copies (a step = one task)
     tasks_per_hour = world * K / (dev_ms / 1e3) * 3600.0
     e2e_tph = world * K / e2e_s * 3600.0
     weights_gb = {"anythingv3": 2 * (859.5 + 123.1 + 49.5) / 1e3, "zeroscopev2xl": 2 * (1411.2 + 340 + 49.5) / 1e3,
@@ -258,7 +259,7 @@ def main() -> int:
                    "l2": f"inputs larger than L2: every task streams {weights_gb:.2f} GB of weights through a 126 MB L2"},
         "clocks": clocks,
         "e2e": {"value": round(e2e_tph, 2), "unit": "tasks/hour", "ms_per_task": round(e2e_s / K * 1e3, 3),
-                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
+                "h2d_bytes_per_step": pipe.h2d_bytes // e2e_group, "d2h_bytes_per_step": pipe.d2h_bytes // e2e_group,
                 "includes": "per task: tokenise, pinned H2D ids, Philox noise, graph replay, D2H pixels, PNG encode, CIDv0"
                             + (" (predict_many: encode of task i overlaps the GPU work of task i+1)"
                                if hasattr(pipe, "predict_many") else ""),
