@@ -99,3 +99,18 @@ def test_frame_parallel_video_matches_single_gpu_bytes():
     sys.stdout.write(r.stdout[-3000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "bit-identical=False" not in r.stdout and "bit-identical=True" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_frame_parallel_predictor_in_one_process_matches_single_gpu_bytes():
+    """The miner's in-process form: one thread per GPU, heaps addressed directly (no IPC), same MP4 bytes."""
+    from arbius_b200.models.registry import build_frame_parallel_predictor, build_predictor
+    inp = {"prompt": "a panda eating bamboo", "negative_prompt": "noisy", "num_frames": 8, "num_inference_steps": 3,
+           "width": 64, "height": 64, "fps": 8, "seed": 5}
+    single = build_predictor("zeroscopev2xl", device="cuda:0", tiny=True)
+    want = single(dict(inp))
+    fp = build_frame_parallel_predictor("zeroscopev2xl", devices=(0, 1), tiny=True)
+    assert fp(dict(inp)) == want
+    assert fp(dict(inp)) == want                         # graph replay
+    assert fp(dict(inp, seed=6)) != want
