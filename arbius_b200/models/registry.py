@@ -180,15 +180,17 @@ def build_pair_predictor(name: str, devices=(0, 1), model_dir: Optional[str] = N
                 with torch.cuda.device(devices[i]):
                     out[i] = pipes[i].predict(dict(inp))
             except BaseException as e:                      # noqa: BLE001 - re-raised on the calling thread
+                import time
+                e._when = time.monotonic()
                 out[i] = e
         threads = [threading.Thread(target=run, args=(i,)) for i in range(2)]
         for t in threads:
             t.start()
         for t in threads:
             t.join()
-        for o in out:
-            if isinstance(o, BaseException):
-                raise o
+        errs = sorted((o for o in out if isinstance(o, BaseException)), key=lambda e: getattr(e, "_when", 0.0))
+        if errs:                                            # the first failure is the cause; a peer's barrier timeout follows it
+            raise errs[0]
         return out[0]
 
     predict.pipelines = pipes
@@ -230,15 +232,17 @@ def build_frame_parallel_predictor(name: str, devices=(0, 1), model_dir: Optiona
                 with torch.cuda.device(devices[i]):
                     out[i] = pipes[i].predict(dict(inp))
             except BaseException as e:                      # noqa: BLE001 - re-raised on the calling thread
+                import time
+                e._when = time.monotonic()
                 out[i] = e
         threads = [threading.Thread(target=run, args=(i,)) for i in range(len(devices))]
         for t in threads:
             t.start()
         for t in threads:
             t.join()
-        for o in out:
-            if isinstance(o, BaseException):
-                raise o
+        errs = sorted((o for o in out if isinstance(o, BaseException)), key=lambda e: getattr(e, "_when", 0.0))
+        if errs:                                            # the first failure is the cause; a peer's barrier timeout follows it
+            raise errs[0]
         return out[0]
 
     predict.pipelines = pipes

@@ -159,10 +159,15 @@ def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
 def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
             x2: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
             rowbias: Optional[torch.Tensor] = None, act: Optional[str] = None, out_scale: float = 1.0,
-            splitk: int = 0, block_n: int = 0) -> torch.Tensor:
-    """3x3 / pad 1 / stride 1 implicit-GEMM conv. x [B,H,W,C1] (+ x2 [B,H,W,C2]), w_packed [Cout, 9*(C1+C2)]."""
+            splitk: int = 0, block_n: int = 0, halo: bool = False) -> torch.Tensor:
+    """3x3 / pad 1 / stride 1 implicit-GEMM conv. x [B,H,W,C1] (+ x2 [B,H,W,C2]), w_packed [Cout, 9*(C1+C2)].
+    ``halo``: x (and x2) are [B, H + 2, W, C] — a row band of the image with the neighbouring bands' edge rows (or zeros
+    at the image's top and bottom) in rows 0 and H+1, as a patch-parallel rank holds it; ``BATCH_SCALE`` then counts
+    the bands, so the split-K choice is the whole image's."""
     lib = native.load()
     b, h, wd, c1 = x.shape
+    if halo:
+        h -= 2
     assert x.is_contiguous() and w_packed.is_contiguous()
     c2 = x2.shape[-1] if x2 is not None else 0
     n = w_packed.shape[0]
@@ -173,15 +178,16 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     a.bias, a.rowbias, a.residual = native.ptr(bias), native.ptr(rowbias), native.ptr(residual)
     a.M, a.N, a.K1, a.K2 = b * h * wd, n, c1, c2
     a.conv, a.nimg, a.H, a.W = 1, b, h, wd
+    a.halo = 1 if halo else 0
     a.act, a.geglu, a.out_scale = ACT[act], 0, out_scale
     a.dtype = native.dtype_code(x.dtype)
     a.block_n = block_n
     a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = 9 * (c1 + c2) // 64
-    key = f"conv:{_canon(b)}x{h}x{wd}:{n}:{c1 + c2}"
+    key = f"conv:{b}x{_canon(h)}x{wd}:{n}:{c1 + c2}" if halo else f"conv:{_canon(b)}x{h}x{wd}:{n}:{c1 + c2}"
     if RECORD is not None:
         RECORD.append(key)
-    cfg = _tuned_pair(key, f"conv:{b}x{h}x{wd}:{n}:{c1 + c2}") if (splitk == 0 and block_n == 0) else None
+    cfg = _tuned_pair(key, key if halo else f"conv:{b}x{h}x{wd}:{n}:{c1 + c2}") if (splitk == 0 and block_n == 0) else None
     if cfg is not None:
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:

@@ -81,11 +81,21 @@ def graph_capture(graph):
     break the capture nor are broken by it. Replays stay concurrent."""
     import torch
     with _CAPTURE_LOCK:
-        # an explicit stream on the CURRENT device: torch.cuda.graph's default capture stream is created once per
-        # process on whichever device was current then, and entering it silently switches devices
+        # An explicit stream on the CURRENT device: torch.cuda.graph's default capture stream is created once per
+        # process on whichever device was current then, and entering it silently switches devices.
+        # capture_begin/capture_end are called directly: the torch.cuda.graph context also empties the caching
+        # allocator on entry, and the cudaFree calls behind that wait for EVERY device of the process to go idle —
+        # while another thread's GPU may be spinning in a peer barrier for this thread (a deadlock until the barrier's
+        # timeout; seen with the in-process pair predictor).
         stream = torch.cuda.Stream(device=torch.cuda.current_device())
-        with torch.cuda.graph(graph, stream=stream, capture_error_mode="thread_local"):
-            yield
+        stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(stream):
+            graph.capture_begin(capture_error_mode="thread_local")
+            try:
+                yield
+            finally:
+                graph.capture_end()
+        torch.cuda.current_stream().wait_stream(stream)
 
 
 def lib_path() -> Path:

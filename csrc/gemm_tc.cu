@@ -639,7 +639,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     p.k1_chunks = (a->K2 > 0 || a->conv) ? a->K1 / BK : (a->K1 + BK - 1) / BK;
     p.k2_chunks = a->K2 > 0 ? (a->conv ? a->K2 / BK : (a->K2 + BK - 1) / BK) : 0;
     p.conv = a->conv; p.nimg = a->nimg; p.H = a->H; p.W = a->W; p.halo = a->halo;
-    AB_REQUIRE(a->halo == 0 || (a->halo == 1 && a->conv == 2 && a->K2 == 0), "halo rows: temporal conv (conv == 2) without virtual concat only");
+    AB_REQUIRE(a->halo == 0 || (a->halo == 1 && a->conv != 0), "halo rows (0 or 1) exist in the conv modes only");
     p.rows_per_group = a->conv ? a->H * a->W : a->rows_per_group;
     p.act = a->act; p.geglu = a->geglu;
     p.out_scale = a->out_scale == 0.f ? 1.f : a->out_scale;
@@ -714,8 +714,8 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         if (ab_make_tensor_map(&tmA, a->dtype, 4, a->a, dims, str, box, 128)) return -1;
         tmA2 = tmA;
         if (a->K2 > 0) {
-            uint64_t dims2[4] = {(uint64_t)a->K2, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
-            uint64_t str2[3] = {(uint64_t)a->K2 * esz, (uint64_t)a->W * a->K2 * esz, (uint64_t)a->H * a->W * a->K2 * esz};
+            uint64_t dims2[4] = {(uint64_t)a->K2, (uint64_t)a->W, Hin, (uint64_t)a->nimg};
+            uint64_t str2[3] = {(uint64_t)a->K2 * esz, (uint64_t)a->W * a->K2 * esz, Hin * a->W * a->K2 * esz};
             if (ab_make_tensor_map(&tmA2, a->dtype, 4, a->a2, dims2, str2, box, 128)) return -1;
         }
     } else {

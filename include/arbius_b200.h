@@ -64,9 +64,11 @@ typedef struct {
   int ldo;                  /* output row stride in elements, 0 = Nout */
   int ldr;                  /* residual row stride in elements, 0 = Nout */
   int ldrb;                 /* rowbias row stride in elements, 0 = N */
-  int halo;                 /* conv == 2 only: A holds `halo` extra rows of H before and after every image
-                             * ([nimg, H + 2*halo, W, K1], H counts output rows): a frame-sharded temporal conv whose
-                             * neighbour frames were copied in from the GPUs next door. 0 or 1. */
+  int halo;                 /* conv modes: A (and A2) hold `halo` extra rows of H before and after every image
+                             * ([nimg, H + 2*halo, W, K], H counts output rows) that are read as data instead of the
+                             * zero padding: a row band of an image (patch parallelism) or the local frames of a clip
+                             * (frame parallelism) with the neighbours' edge rows copied in from the GPUs next door.
+                             * 0 or 1. */
 } ab_gemm_args;
 int ab_gemm(const ab_gemm_args* args, void* stream);
 /* Multi-GPU forms of the same kernel (one NVSwitch box; pointers may be peer-mapped addresses).

@@ -112,3 +112,33 @@ def test_peer_copy2d_strided_and_zero_fill():
     assert torch.equal(dst[:, 1], src[:, 4]) and (dst[:, 0] == -1).all() and (dst[:, 2] == -1).all()
     assert lib.ab_peer_copy2d(dst[:, 2].data_ptr(), 3 * 128, None, 0, 128, 4, ops.native.stream_ptr()) == 0
     assert (dst[:, 2] == 0).all() and torch.equal(dst[:, 1], src[:, 4])
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("concat", [False, True])
+def test_halo_conv3x3_row_bands_match_undivided_bytes(world, concat):
+    """Patch parallelism's conv: every rank holds a row band of the image plus one halo row above and below."""
+    ops = _ops()
+    from arbius_b200.ops import gemm as gemm_mod
+    b, h, wd, c, n = 2, 32, 32, 128, 192
+    torch.manual_seed(3)
+    x = torch.randn(b, h, wd, c, device="cuda").half()
+    x2 = torch.randn(b, h, wd, 64, device="cuda").half() if concat else None
+    cin = c + (64 if concat else 0)
+    w = ops.pack_conv_weight((torch.randn(n, cin, 3, 3, device="cuda") * 0.03).half())
+    bias = torch.randn(n, device="cuda").half()
+    ref = ops.conv3x3(x, w, bias, x2=x2, act="silu")
+    hl = h // world
+
+    def band(t, r):
+        z = torch.zeros(b, 1, wd, t.shape[-1], dtype=t.dtype, device="cuda")
+        top = t[:, r * hl - 1:r * hl] if r > 0 else z
+        bot = t[:, (r + 1) * hl:(r + 1) * hl + 1] if r < world - 1 else z
+        return torch.cat([top, t[:, r * hl:(r + 1) * hl], bot], 1).contiguous()
+    gemm_mod.BATCH_SCALE = world
+    try:
+        for r in range(world):
+            got = ops.conv3x3(band(x, r), w, bias, x2=band(x2, r) if concat else None, act="silu", halo=True)
+            assert torch.equal(got, ref[:, r * hl:(r + 1) * hl]), f"rank {r}"
+    finally:
+        gemm_mod.BATCH_SCALE = 1
