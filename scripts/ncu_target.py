@@ -16,6 +16,11 @@ elif what == "conv":
         x = torch.randn(b_, h, w_, ci, device="cuda", dtype=dt); wt = torch.randn(co, 9 * ci, device="cuda", dtype=dt); b = torch.randn(co, device="cuda", dtype=dt)
         for _ in range(3):
             ops.conv3x3(x, wt, b, block_n=bn, splitk=1)
+elif what == "convb":      # the UNet's 32x32 level at four tasks per replay (batch 8): the largest share of the batched task
+    for (b_, h, w_, ci, co, bn, sk) in [(8, 32, 32, 1280, 1280, 160, 2), (8, 64, 64, 640, 640, 160, 1)]:
+        x = torch.randn(b_, h, w_, ci, device="cuda", dtype=dt); wt = torch.randn(co, 9 * ci, device="cuda", dtype=dt) / (9 * ci) ** 0.5; b = torch.randn(co, device="cuda", dtype=dt)
+        for _ in range(3):
+            ops.conv3x3(x, wt, b, block_n=bn, splitk=sk)
 elif what == "attn":
     shape = (2, 9216, 5, 64) if (len(sys.argv) > 2 and sys.argv[2] == "video") else (2, 4096, 8, 40)
     q = torch.randn(*shape, device="cuda", dtype=dt); k = torch.randn_like(q); v = torch.randn_like(q)
