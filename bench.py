@@ -248,7 +248,7 @@ def main() -> int:
     weights_gb = {"anythingv3": 2 * (859.5 + 123.1 + 49.5) / 1e3, "zeroscopev2xl": 2 * (1411.2 + 340 + 49.5) / 1e3,
                   "damo": 2 * (1411.2 + 340 + 49.5) / 1e3}.get(args.model, 0.0)
     out = {
-        "metric": METRIC if not video else f"tasks/hour + p50 task latency ({model_desc})", "value": round(tasks_per_hour, 2), "unit": "tasks/hour", "impl": args.impl,
+        "metric": METRIC if args.model in ("anythingv3", "tiny") else f"tasks/hour + p50 task latency ({model_desc})", "value": round(tasks_per_hour, 2), "unit": "tasks/hour", "impl": args.impl,
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(dev_ms / K, 3),
         "p50_latency_ms": round(lat_ms[len(lat_ms) // 2], 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
