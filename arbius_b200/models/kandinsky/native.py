@@ -165,15 +165,18 @@ class _KAttn:
         for i in range(b):
             ops.gemm(enc[i], self.wekv, self.bekv, out=self.buf[i, :t, c:], splitk=1)
 
+    off = 0                                    # first sample of the batch held here (guidance parallelism: the rank)
+
     def __call__(self, x: torch.Tensor) -> torch.Tensor:
         b, hh, ww, c = x.shape
         l, h, t = hh * ww, self.heads, self.t
         n = ops.groupnorm(x, *self.norm, self.groups, 1e-5, None).view(b, l, c)
+        buf = self.buf[self.off:self.off + b]
         for i in range(b):
-            ops.gemm(n[i], self.wqkv, self.bqkv, out=self.buf[i, t:], splitk=1)
-        q = self.buf[:, t:, :c].view(b, l, h, c // h)
-        k = self.buf[:, :, c:2 * c].view(b, t + l, h, c // h)
-        v = self.buf[:, :, 2 * c:].view(b, t + l, h, c // h)
+            ops.gemm(n[i], self.wqkv, self.bqkv, out=buf[i, t:], splitk=1)
+        q = buf[:, t:, :c].view(b, l, h, c // h)
+        k = buf[:, :, c:2 * c].view(b, t + l, h, c // h)
+        v = buf[:, :, 2 * c:].view(b, t + l, h, c // h)
         a = ops.flash_attn(q, k, v)
         return ops.gemm(a.view(b * l, c), self.wo, self.bo, residual=x.view(b * l, c)).view(b, hh, ww, c)
 
@@ -290,8 +293,10 @@ class NativeKandinskyUNet:
                 h = m(h)
         return h
 
-    def forward(self, x: torch.Tensor, emb_all: torch.Tensor) -> torch.Tensor:
-        """x [B, H, W, 4] -> [B, H, W, 8]."""
+    def forward(self, x: torch.Tensor, emb_all: torch.Tensor, sample_offset: int = 0) -> torch.Tensor:
+        """x [B, H, W, 4] -> [B, H, W, 8]. ``sample_offset``: x holds samples [offset, offset+B) of the prepared batch."""
+        for a in self.attn:
+            a.off = sample_offset
         h = ops.conv_direct(x, *self.conv_in)
         hs = [h]
         for blk in self.input_blocks:

@@ -47,8 +47,14 @@ class Kandinsky2Config:
 
 class Kandinsky2Pipeline:
     def __init__(self, cfg: Kandinsky2Config = Kandinsky2Config(), backend: str = "native", device: str = "cuda",
-                 dtype=torch.float16, seed: int = 0, model_dir: Optional[str] = None, use_graph: bool = True):
+                 dtype=torch.float16, seed: int = 0, model_dir: Optional[str] = None, use_graph: bool = True,
+                 cfg_parallel=None):
+        """``cfg_parallel``: a 2-rank ``PeerHeap`` — the two classifier-free-guidance branches of every decoder-UNet step
+        run on two GPUs and exchange their predictions through peer memory (as in ``SD15Pipeline``); text encoder,
+        prior and MoVQ are small and run whole on both. Same bytes as one GPU."""
         self.cfg, self.backend, self.device, self.dtype = cfg, backend, torch.device(device), dtype
+        self.cfgp = cfg_parallel
+        assert cfg_parallel is None or (cfg_parallel.world == 2 and backend == "native"), "cfg_parallel needs a 2-rank heap"
         self.tokenizer = HashTokenizer(cfg.text.vocab_size, 77)
         with torch.device(device):
             unet, prior = KandinskyUNet(cfg.unet), DiffusionPrior(cfg.prior, text_dim=cfg.text.hidden)
@@ -160,12 +166,37 @@ class Kandinsky2Pipeline:
             for b in range(2):
                 ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=sch.input_scale(i))
             emb_all = self.unet.embeddings(st["tvec"][2 * i:2 * i + 2], cond)
-            e = self.unet.forward(st["xin"], emb_all)
-            ops.cfg_step(e[1], e[0], None, g=c.guidance, eps_out=f["eps"])
+            if self.cfgp is None:
+                e = self.unet.forward(st["xin"], emb_all)
+                ops.cfg_step(e[1], e[0], None, g=c.guidance, eps_out=f["eps"])
+            else:
+                self._cfg_parallel_step(st, i, emb_all)
             for dst, terms in sch.plan(i):
                 ops.lincomb(f[dst], [(co, st["noise"][i] if s == "noise" else f[s]) for co, s in terms])
         ops.lincomb(None, [(1.0, f["x"])], dst_m=st["lat"], m_scale=1.0)
         st["u8"] = ops.finalize_u8(self.movq.forward(st["lat"]))
+
+    def _cfg_parallel_step(self, st: dict, i: int, emb_all) -> None:
+        """This rank's guidance branch of decoder step i; predictions cross through two parity slots in the peer heap
+        behind one device barrier per step (see SD15Pipeline._cfg_parallel_step)."""
+        import sys
+        heap, r, par = self.cfgp, self.cfgp.rank, i & 1
+        gemm_mod = sys.modules["arbius_b200.ops.gemm"]
+        gemm_mod.BATCH_SCALE = 2                      # split-K choices of the undivided batch of two
+        try:
+            e = self.unet.forward(st["xin"][r:r + 1], emb_all[r:r + 1], sample_offset=r)
+        finally:
+            gemm_mod.BATCH_SCALE = 1
+        slot = st["ex"][par]
+        slot.copy_(e)
+        heap.barrier_replayable()
+        own = slot.data_ptr()
+        peer = heap.peer_ptr(1 - r, st["ex_off"] + par * slot.numel() * slot.element_size())
+        ptr_c, ptr_u = (own, peer) if r == 1 else (peer, own)
+        lib = ops.native.load()
+        ops.native.check(lib.ab_cfg_step(ptr_c, ptr_u, None, None, None, None, None, st["f32"]["eps"].data_ptr(),
+                                         slot.numel(), self.cfg.guidance, 0.0, 1.0, 0.0, 0.0,
+                                         ops.native.dtype_code(slot.dtype), ops.native.stream_ptr()), "ab_cfg_step")
 
     def _native(self, ids, width, height, seed) -> np.ndarray:
         c, dev, dt = self.cfg, self.device, self.dtype
@@ -193,6 +224,8 @@ class Kandinsky2Pipeline:
                       image_emb=torch.zeros((2, c.prior.clip_dim), dtype=dt, device=dev),
                       xin=torch.zeros((2, h, w, 4), dtype=dt, device=dev), lat=torch.zeros(shape, dtype=dt, device=dev),
                       out_host=torch.zeros((height, width, 3), dtype=torch.uint8).pin_memory(), graph=None, launches=0)
+            if self.cfgp is not None:
+                st["ex"], st["ex_off"] = self.cfgp.alloc((2, 1, h, w, 4), dt)      # same offset on both ranks
             if self.use_graph:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())

@@ -139,7 +139,7 @@ class BatchingPredictor:
 
 
 BATCH_FAMILIES = ("anythingv3",)
-PAIR_FAMILIES = ("anythingv3", "zeroscopev2xl", "damo")
+PAIR_FAMILIES = ("anythingv3", "kandinsky2", "zeroscopev2xl", "damo")
 
 
 def build_pair_predictor(name: str, devices=(0, 1), model_dir: Optional[str] = None, tiny: bool = False,
@@ -165,6 +165,10 @@ def build_pair_predictor(name: str, devices=(0, 1), model_dir: Optional[str] = N
                 from .sd15.pipeline import SD15Config, SD15Pipeline
                 pipes.append(SD15Pipeline(SD15Config.tiny() if tiny else SD15Config(), backend="native", device=f"cuda:{d}",
                                           dtype=dtype, model_dir=model_dir, cfg_parallel=heap))
+            elif name == "kandinsky2":
+                from .kandinsky.pipeline import Kandinsky2Config, Kandinsky2Pipeline
+                pipes.append(Kandinsky2Pipeline(Kandinsky2Config.tiny() if tiny else Kandinsky2Config(), backend="native",
+                                                device=f"cuda:{d}", dtype=dtype, model_dir=model_dir, cfg_parallel=heap))
             else:
                 from .video.pipeline import TextToVideoConfig, TextToVideoPipeline
                 cfg = TextToVideoConfig.tiny() if tiny else (TextToVideoConfig.zeroscope_xl() if name == "zeroscopev2xl"

@@ -332,8 +332,6 @@ class SD15Pipeline:
                 j = i + 1
                 while j < len(tasks) and j - i < task_batch and shape_key(tasks[j]) == shape_key(tasks[i]):
                     j += 1
-                if j - i < task_batch:
-                    j = i + 1                          # partial groups run singly: one graph per batch size in use
                 imgs = self.generate_batch(tasks[i:j])
                 futs += [pool.submit(encode_png, img) for img in imgs]
                 i = j

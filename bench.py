@@ -83,7 +83,7 @@ class ClockSampler:
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=8, help="timed tasks per GPU")
+    ap.add_argument("--steps", type=int, default=9, help="timed tasks per GPU")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "eager", "reference"])
     ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "tiny", "zeroscopev2xl", "damo", "video-tiny",
@@ -93,7 +93,7 @@ def main() -> int:
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--latency-mode", action="store_true",
                     help="with >= 2 GPUs also time guidance-parallel pairs (one task over two GPUs) and add 'latency_mode'")
-    ap.add_argument("--task-batch", type=int, default=4,
+    ap.add_argument("--task-batch", type=int, default=3,
                     help="independent tasks per graph replay (anythingv3 native only); bytes per task do not change")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -169,10 +169,10 @@ def main() -> int:
     counted = [0]
 
     def run_tasks(seeds):
-        """The timed unit: len(seeds) tasks, TB per graph replay (a remainder runs singly). Returns per-task event pairs."""
+        """The timed unit: len(seeds) tasks, TB per graph replay. Returns per-task event pairs."""
         evs, i = [], 0
         while i < len(seeds):
-            n = TB if len(seeds) - i >= TB else 1
+            n = min(TB, len(seeds) - i)                # a shorter last group is one (smaller) batch too
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             if n == 1:
@@ -191,6 +191,8 @@ def main() -> int:
     if TB > 1:
         for i in range(W):
             run_tasks([1500 + rank * 100 + i * TB + j for j in range(TB)])
+            if K % TB > 1:                             # the last group's batch size needs its graph too
+                run_tasks([1700 + rank * 100 + i * TB + j for j in range(K % TB)])
     barrier()
 
     # ---- device-timed region: K tasks, CUDA events on the launching stream ----
@@ -242,7 +244,7 @@ def main() -> int:
     e2e_s = reduce_max(time.perf_counter() - t0)
     barrier()
 
-    e2e_group = TB if (TB > 1 and K % TB == 0) else 1      # tasks behind the last replay's copies (a step = one task)
+    e2e_group = (K % TB or TB) if TB > 1 else 1            # tasks behind the last replay's copies (a step = one task)
     tasks_per_hour = world * K / (dev_ms / 1e3) * 3600.0
     e2e_tph = world * K / e2e_s * 3600.0
     weights_gb = {"anythingv3": 2 * (859.5 + 123.1 + 49.5) / 1e3, "zeroscopev2xl": 2 * (1411.2 + 340 + 49.5) / 1e3,

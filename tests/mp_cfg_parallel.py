@@ -60,6 +60,42 @@ def main():
         t_ref = timeit(full_ref)
         if rank == 0:
             print(f"RESULT cfg_parallel world=2 latency_ms={t_par:.2f} single_gpu_latency_ms={t_ref:.2f}", flush=True)
+    # ---------------- Kandinsky 2.1 ----------------
+    from arbius_b200.models.kandinsky.pipeline import Kandinsky2Config, Kandinsky2Pipeline
+    kref = Kandinsky2Pipeline(Kandinsky2Config.tiny(), backend="native", device=dev, dtype=torch.float16)
+    kpar = Kandinsky2Pipeline(Kandinsky2Config.tiny(), backend="native", device=dev, dtype=torch.float16, cfg_parallel=heap)
+    a = kref.generate("arbius test cat", 32, 32, seed=5)
+    b1 = kpar.generate("arbius test cat", 32, 32, seed=5)
+    b2 = kpar.generate("arbius test cat", 32, 32, seed=5)
+    same = bool((a == b1).all() and (a == b2).all())
+    print(f"rank {rank} kandinsky-tiny bit-identical={same}", flush=True)
+    ok = ok and same
+    if os.environ.get("AB_CFGP_FULL", "1") == "1":
+        del kref, kpar
+        torch.cuda.empty_cache()
+        kref = Kandinsky2Pipeline(Kandinsky2Config(), backend="native", device=dev, dtype=torch.float16)
+        kpar = Kandinsky2Pipeline(Kandinsky2Config(), backend="native", device=dev, dtype=torch.float16, cfg_parallel=heap)
+        a = kref.generate("arbius test cat", 768, 768, seed=5)
+        b = kpar.generate("arbius test cat", 768, 768, seed=5)
+        same = bool((a == b).all())
+        print(f"rank {rank} Kandinsky 2.1 768x768 bit-identical={same}", flush=True)
+        ok = ok and same
+
+        def ktime(p, n=3):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            for i in range(n):
+                p.generate("arbius test cat", 768, 768, seed=30 + i)
+            torch.cuda.synchronize()
+            t = torch.tensor([(time.perf_counter() - t0) / n * 1e3], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.item()
+        t_par, t_ref = ktime(kpar), ktime(kref)
+        if rank == 0:
+            print(f"RESULT kandinsky2 cfg_parallel world=2 latency_ms={t_par:.1f} single_gpu_latency_ms={t_ref:.1f}", flush=True)
+        del kref, kpar
+        torch.cuda.empty_cache()
     # ---------------- text-to-video UNet3D ----------------
     from arbius_b200.models.video.pipeline import TextToVideoConfig, TextToVideoPipeline
     vref = TextToVideoPipeline(TextToVideoConfig.tiny(), backend="native", device=dev, dtype=torch.float16, family="video-tiny")
