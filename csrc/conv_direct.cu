@@ -61,16 +61,26 @@ __global__ void __launch_bounds__(256) conv_few_in_kernel(const T* __restrict__ 
     }
 }
 
-template <typename T, int MAXCO>
+template <typename T, int MAXCO, bool SMEM_W>
 __global__ void __launch_bounds__(256) conv_few_out_kernel(const T* __restrict__ x, const T* __restrict__ w,
                                                            const T* __restrict__ bias, T* __restrict__ out, int n, int h,
                                                            int wd, int cin, int cout, int ks, int stride, int ho, int wo,
                                                            int act) {
+    // The whole weight tensor (cout x ks*ks*cin, <= 48 KB for the UNet/VAE output convs) is staged in shared memory once
+    // per block when it fits: every pixel re-reads all of it, and from global memory that re-read is the kernel's
+    // traffic. Same values, same order of operations: the result bits do not change.
+    extern __shared__ uint4 w_smem[];
     const int lane = threadIdx.x & 31;
     const int warps_per_block = blockDim.x >> 5;
     const int pad = ks / 2;
     const int vec_per_tap = cin / 8;
     const int kk = ks * ks * cin;
+    if (SMEM_W) {
+        const uint4* wg = reinterpret_cast<const uint4*>(w);
+        for (int i = threadIdx.x; i < cout * kk / 8; i += blockDim.x) w_smem[i] = __ldg(wg + i);
+        __syncthreads();
+        w = reinterpret_cast<const T*>(w_smem);
+    }
     const long long total = static_cast<long long>(n) * ho * wo;
     for (long long pix = static_cast<long long>(blockIdx.x) * warps_per_block + (threadIdx.x >> 5); pix < total;
          pix += static_cast<long long>(gridDim.x) * warps_per_block) {
@@ -93,7 +103,8 @@ __global__ void __launch_bounds__(256) conv_few_out_kernel(const T* __restrict__
                 for (int j = 0; j < MAXCO; ++j) {
                     if (j < cout) {
                         float wv[8];
-                        unpack8<T>(__ldg(reinterpret_cast<const uint4*>(pw + static_cast<long long>(j) * kk + v * 8)), wv);
+                        const uint4* wp = reinterpret_cast<const uint4*>(pw + static_cast<long long>(j) * kk + v * 8);
+                        unpack8<T>(SMEM_W ? *wp : __ldg(wp), wv);
 #pragma unroll
                         for (int i = 0; i < 8; ++i) acc[j] = fmaf(f[i], wv[i], acc[j]);
                     }
@@ -131,10 +142,15 @@ extern "C" int ab_conv_direct(const void* x, const void* w, const void* bias, vo
     const long long work = few_out ? (static_cast<long long>(n) * ho * wo + 7) / 8
                                    : (static_cast<long long>(n) * ho * wo * (cout / 8) + threads - 1) / threads;
     const int blocks = static_cast<int>(std::min<long long>(std::max<long long>(work, 1), 148LL * 8));
+    const size_t w_bytes = static_cast<size_t>(cout) * ksize * ksize * cin * 2;
 #define AB_LAUNCH(T)                                                                                               \
     do {                                                                                                           \
-        if (few_out)                                                                                               \
-            conv_few_out_kernel<T, 8><<<blocks, threads, 0, stream>>>(                                             \
+        if (few_out && w_bytes <= 48 * 1024)                                                                       \
+            conv_few_out_kernel<T, 8, true><<<blocks, threads, w_bytes, stream>>>(                                 \
+                reinterpret_cast<const T*>(x), reinterpret_cast<const T*>(w), reinterpret_cast<const T*>(bias),    \
+                reinterpret_cast<T*>(out), n, h, wd, cin, cout, ksize, stride, ho, wo, act);                       \
+        else if (few_out)                                                                                          \
+            conv_few_out_kernel<T, 8, false><<<blocks, threads, 0, stream>>>(                                      \
                 reinterpret_cast<const T*>(x), reinterpret_cast<const T*>(w), reinterpret_cast<const T*>(bias),    \
                 reinterpret_cast<T*>(out), n, h, wd, cin, cout, ksize, stride, ho, wo, act);                       \
         else                                                                                                       \
