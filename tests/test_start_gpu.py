@@ -30,7 +30,7 @@ def test_native_config_builds_subset_predictors_and_widens_a_lone_video_task(tmp
     node.bootup()
     node.run_until_idle()
     inp = {"prompt": "a panda eating bamboo", "negative_prompt": "noisy", "num_frames": 8, "num_inference_steps": 2,
-           "width": 64, "height": 64}
+           "width": 256, "height": 256}
     mid = ids["zeroscopev2xl"]
     tid = eng.submit_task(node.chain.address, 0, node.chain.address, mid, 0, json.dumps(inp, separators=(",", ":")).encode())
     node.run_until_idle()
