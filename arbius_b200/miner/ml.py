@@ -191,12 +191,15 @@ class NativeBackend(MLBackend):
                     lk.acquire_all()
                 try:
                     out = sub(inp)
+                except MemoryError:
+                    out = None                        # the subset's peer heap is too small for this request: one GPU does it
                 finally:
                     for lk in reversed(locks):
                         lk.release_all()
                 if isinstance(out, (bytes, bytearray)):
                     out = {output_filename(model.template): bytes(out)}
-                return out
+                if out is not None:
+                    return out
         if endpoint is None and gpus:
             endpoint = gpus[0]
         if endpoint is None:

@@ -219,7 +219,9 @@ def build_frame_parallel_predictor(name: str, devices=(0, 1), model_dir: Optiona
         raise ValueError(f"{name!r} has no frame-parallel form; choices: {FRAME_FAMILIES}")
     assert len(devices) in (2, 4, 8)
     dtype = dtype or torch.float16
-    heaps = PeerHeap.local_group(heap_bytes or ((256 << 20) if tiny else (3 << 30)), devices)
+    # sized for the template's largest default clip (ZeroScope XL 1024x576x24 needs 1.4 GB); a request that does not
+    # fit raises MemoryError on every rank before the first barrier, and the miner falls back to one GPU
+    heaps = PeerHeap.local_group(heap_bytes or ((1 << 30) if tiny else (3 << 30)), devices)
     cfg = TextToVideoConfig.tiny() if tiny else (TextToVideoConfig.zeroscope_xl() if name == "zeroscopev2xl"
                                                   else TextToVideoConfig.damo())
     pipes = []

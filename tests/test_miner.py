@@ -392,3 +392,14 @@ def test_cost_table_widens_video_tasks_over_idle_gpus():
     assert CostModel.measured_b200([], ["zeroscopev2xl"], [2]).best_latency_p("zeroscopev2xl", 8) == 2
     sim = simulate([(0.0, "zeroscopev2xl")], 8, cost, "latency")
     assert abs(sim["p50_latency_s"] - 2.768) < 1e-6
+
+
+def test_subset_predictor_out_of_heap_falls_back_to_one_gpu():
+    eng, node, mid, _ = _setup()
+    model = node.models[0]
+
+    def too_big(inp):
+        raise MemoryError("peer heap exhausted")
+    ml = NativeBackend({mid: [lambda inp: FIXED_PNG + b"0", lambda inp: FIXED_PNG + b"1"]}, {mid: {(0, 1): too_big}})
+    assert ml.getfiles(model, "0x0", {"seed": 1}, gpus=(0, 1)) == {"out-1.png": FIXED_PNG + b"0"}
+    assert not any(lk.locked() for lk in ml._locks[mid.lower()])

@@ -27,6 +27,7 @@ def test_native_config_builds_subset_predictors_and_widens_a_lone_video_task(tmp
     assert node.pool.planner.n == 2 and node.pool.planner.slots == 2
     assert set(node.ml.subset_sizes(next(m for m in node.models if m.name == "zeroscopev2xl"))) == {1, 2}
     eng = node.chain.engine
+    node._retry_sleep = lambda s: None                                     # a failure should fail fast here
     node.bootup()
     node.run_until_idle()
     inp = {"prompt": "a panda eating bamboo", "negative_prompt": "noisy", "num_frames": 8, "num_inference_steps": 2,
