@@ -226,6 +226,8 @@ class Kandinsky2Pipeline:
                       out_host=torch.zeros((height, width, 3), dtype=torch.uint8).pin_memory(), graph=None, launches=0)
             if self.cfgp is not None:
                 st["ex"], st["ex_off"] = self.cfgp.alloc((2, 1, h, w, 4), dt)      # same offset on both ranks
+            if self.cfgp is not None:
+                self.cfgp.dry_run(lambda: self._run_native(st))
             if self.use_graph:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())

@@ -236,6 +236,8 @@ class SD15Pipeline:
                   graph=None, launches=0)
         if self.cfgp is not None:
             st["ex"], st["ex_off"] = self.cfgp.alloc((2, 1, h, w, 4), dt)      # same offset on both ranks
+        if self.cfgp is not None:
+            self.cfgp.dry_run(lambda: self._run_native(st, sch, g))
         if self.use_graph:
             # warm-up run on a side stream (allocator + lazy kernel attribute setup), then capture
             s = torch.cuda.Stream()

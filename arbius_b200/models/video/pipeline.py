@@ -245,6 +245,14 @@ class TextToVideoPipeline:
                 self.unet.set_frame_shard(self._shard)
                 st["clip"], st["clip_off"] = self.fp.alloc((nf, height, width, 3), torch.uint8)
                 self._graphs.clear()                   # the heap was laid out anew: older states' buffers are gone
+            heaps = [hp for hp in (self.cfgp, self.fp) if hp is not None]
+            if len(heaps) == 2:
+                heaps[1].dry = getattr(heaps[1], "_local", False)      # one dry pass with BOTH groups' barriers off
+            if heaps:
+                try:
+                    heaps[0].dry_run(lambda: self._run_native(st, g))
+                finally:
+                    heaps[-1].dry = False
             if self.use_graph:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())

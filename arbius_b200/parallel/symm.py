@@ -119,12 +119,35 @@ class PeerHeap:
         native.check(_lib().ab_peer_barrier(arr, self.rank, self.world, self._epoch, native.stream_ptr()),
                      "ab_peer_barrier")
 
+    dry = False          # set by ``dry_run``: barriers are skipped so that no kernel of this process spins
+
     def barrier_replayable(self) -> None:
         """Device-side barrier whose epoch lives in device memory: safe to capture in a CUDA graph and replay."""
-        if self.world == 1:
+        if self.world == 1 or self.dry:
             return
         arr = (C.c_void_p * self.world)(*self.ptrs)
         native.check(_lib().ab_peer_barrier_auto(arr, self.rank, self.world, native.stream_ptr()), "ab_peer_barrier_auto")
+
+    def dry_run(self, fn) -> None:
+        """In-process groups only (one thread per GPU): run ``fn`` once with the barriers switched off, then meet the
+        other ranks' threads on the host. The first launch of a kernel loads its module (and sets its attributes) under
+        a process-wide lock and waits for the launching GPU to go idle; with two GPUs of one process spinning in a peer
+        barrier for each other, two such first launches deadlock. After the dry pass every kernel variant, allocation
+        and attribute the real pass needs exists, so nothing blocks while a peer spins. Separate processes have separate
+        loaders and do not need this (no-op)."""
+        if not getattr(self, "_local", False):
+            return
+        self.dry = True
+        try:
+            fn()
+            # the barrier kernel itself: one self-only launch loads it (every rank does this once, so the device-side
+            # epochs stay equal; the value it leaves in slot 0 is below every later epoch)
+            arr = (C.c_void_p * 1)(self.base)
+            native.check(_lib().ab_peer_barrier_auto(arr, 0, 1, native.stream_ptr()), "ab_peer_barrier_auto")
+            torch.cuda.synchronize()
+        finally:
+            self.dry = False
+        self._tbar.wait(600)
 
     @classmethod
     def local_group(cls, nbytes: int, devices: Sequence[int]) -> List["PeerHeap"]:
@@ -149,8 +172,11 @@ class PeerHeap:
                 if a != b:
                     assert torch.cuda.can_device_access_peer(a, b), f"no peer access {a} -> {b}"
                     torch.empty(1, device=f"cuda:{a}").copy_(torch.empty(1, device=f"cuda:{b}"))
+        import threading
+        tbar = threading.Barrier(len(devices))
         for h in heaps:
             h.ptrs = [x.base for x in heaps]
+            h._tbar = tbar
         torch.cuda.synchronize()
         return heaps
 
