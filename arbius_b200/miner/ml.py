@@ -191,8 +191,12 @@ class NativeBackend(MLBackend):
                     lk.acquire_all()
                 try:
                     out = sub(inp)
-                except MemoryError:
-                    out = None                        # the subset's peer heap is too small for this request: one GPU does it
+                except (MemoryError, ValueError) as e:
+                    # the subset's peer heap is too small for this request, or its shape does not shard over the
+                    # subset (models/video/pipeline.py UnsupportedSplit): one GPU does it
+                    if isinstance(e, ValueError) and type(e).__name__ != "UnsupportedSplit":
+                        raise
+                    out = None
                 finally:
                     for lk in reversed(locks):
                         lk.release_all()

@@ -49,6 +49,23 @@ class TextToVideoConfig:
                                  default_frames=8, default_fps=8)
 
 
+class UnsupportedSplit(ValueError):
+    """This task's shape cannot be spread over the ranks it was given (the caller should use one GPU)."""
+
+
+def frame_split_ok(nf: int, h: int, w: int, ranks: int, levels: int = 4) -> bool:
+    """Frames must divide over the ranks, 2..128 frames fit one temporal-attention tile, and at every UNet level the
+    rows a rank holds (frames/ranks x pixels) must split evenly into its 8/ranks canonical GroupNorm shards."""
+    if ranks not in (2, 4, 8) or nf % ranks or not 2 <= nf <= 128:
+        return False
+    per = 8 // ranks
+    for _ in range(levels):
+        if ((nf // ranks) * h * w) % per:
+            return False
+        h, w = (h + 1) // 2, (w + 1) // 2
+    return True
+
+
 class TextToVideoPipeline:
     def __init__(self, cfg: TextToVideoConfig, backend: str = "native", device: str = "cuda", dtype=torch.float16,
                  seed: int = 0, model_dir: Optional[str] = None, family: str = "zeroscopev2xl", use_graph: bool = True,
@@ -217,7 +234,9 @@ class TextToVideoPipeline:
         key = (nf, steps, width, height, g, sched)
         P = self.fp.world if self.fp is not None else 1
         rank = self.fp.rank if self.fp is not None else 0
-        assert nf % P == 0, "frames must divide over the frame-parallel ranks"
+        if P > 1 and not frame_split_ok(nf, h, w, P, len(self.cfg.unet.block_out_channels)):
+            # raised on every rank before the first barrier; the miner's backend then runs the task on one GPU
+            raise UnsupportedSplit(f"{nf} frames of {h}x{w} latents do not shard over {P} ranks")
         nfl = nf // P
         st = self._graphs.get(key)
         if st is None:

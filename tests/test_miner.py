@@ -403,3 +403,21 @@ def test_subset_predictor_out_of_heap_falls_back_to_one_gpu():
     ml = NativeBackend({mid: [lambda inp: FIXED_PNG + b"0", lambda inp: FIXED_PNG + b"1"]}, {mid: {(0, 1): too_big}})
     assert ml.getfiles(model, "0x0", {"seed": 1}, gpus=(0, 1)) == {"out-1.png": FIXED_PNG + b"0"}
     assert not any(lk.locked() for lk in ml._locks[mid.lower()])
+
+
+def test_subset_predictor_unsupported_shape_falls_back_but_other_errors_propagate():
+    from arbius_b200.models.video.pipeline import UnsupportedSplit
+    eng, node, mid, _ = _setup()
+    model = node.models[0]
+
+    def no_split(inp):
+        raise UnsupportedSplit("10 frames over 4 ranks")
+
+    def broken(inp):
+        raise ValueError("bad weights")
+    ml = NativeBackend({mid: [lambda inp: FIXED_PNG, lambda inp: FIXED_PNG]}, {mid: {(0, 1): no_split}})
+    assert ml.getfiles(model, "0x0", {"seed": 1}, gpus=(0, 1)) == {"out-1.png": FIXED_PNG}
+    ml = NativeBackend({mid: [lambda inp: FIXED_PNG, lambda inp: FIXED_PNG]}, {mid: {(0, 1): broken}})
+    with pytest.raises(ValueError, match="bad weights"):
+        ml.getfiles(model, "0x0", {"seed": 1}, gpus=(0, 1))
+    assert not any(lk.locked() for lk in ml._locks[mid.lower()])

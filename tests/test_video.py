@@ -62,3 +62,12 @@ def test_eager_video_pipeline_cpu():
     assert a.shape == (4, 32, 32, 3) and a.dtype == np.uint8 and (a == b).all()
     mp4 = pipe.predict({"prompt": "x", "num_frames": 4, "num_inference_steps": 2, "width": 32, "height": 32, "fps": 8, "seed": 1})
     assert mp4[4:8] == b"ftyp" and len(demux_samples(mp4)) == 4
+
+
+def test_frame_split_rules():
+    from arbius_b200.models.video.pipeline import frame_split_ok
+    assert all(frame_split_ok(24, 72, 128, p) for p in (2, 4, 8))          # ZeroScope XL default clip
+    assert all(frame_split_ok(16, 32, 32, p) for p in (2, 4, 8))           # DAMO default clip
+    assert not frame_split_ok(10, 72, 128, 4) and not frame_split_ok(24, 72, 128, 3)
+    assert not frame_split_ok(200, 72, 128, 8)                              # more frames than one attention tile holds
+    assert frame_split_ok(8, 4, 4, 2) and not frame_split_ok(2, 3, 3, 2)   # 1 frame x 9 px does not split into 4 shards
