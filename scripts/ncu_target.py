@@ -42,3 +42,17 @@ if what == "tattn":
         temporal_attn(q, k, v, heads)
     torch.cuda.synchronize()
     print("ok")
+if what == "tattn_ms":     # the frame-parallel form on one GPU: two sources of 12 frames each, rank 0's pixel band
+    from arbius_b200.ops.temporal import temporal_attn_ptrs
+    b, f, hw, heads, d, world = 2, 24, 9216, 5, 64, 2
+    c = heads * d
+    srcs = [torch.randn(b, f // world, hw, 3 * c, device="cuda", dtype=dt) for _ in range(world)]
+    outs = [torch.zeros(b, f // world, hw, c, device="cuda", dtype=dt) for _ in range(world)]
+    qp = [s.data_ptr() for s in srcs]
+    px = 128 // f
+    per = ((hw + px - 1) // px + world - 1) // world
+    for _ in range(3):
+        temporal_attn_ptrs(qp, [p + c * 2 for p in qp], [p + 2 * c * 2 for p in qp], [o.data_ptr() for o in outs],
+                           b, f, hw, heads, d, 3 * c, c, dt, pix_begin=0, pix_count=min(hw, per * px))
+    torch.cuda.synchronize()
+    print("ok")
