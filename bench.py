@@ -26,7 +26,8 @@ def reference_arm() -> int:
     why = ("mainnet-pat/arbius has no Python package or GPU code (TypeScript miner + Solidity; models run in "
            "external Cog containers by docker digest): pip install of /root/reference fails "
            "('neither setup.py nor pyproject.toml'), node/docker/network are absent")
-    print(json.dumps({"impl": "reference", "unavailable": why}))
+    if int(os.environ.get("RANK", "0")) == 0:               # one line per job, also when launched through torchrun
+        print(json.dumps({"impl": "reference", "unavailable": why}))
     return 0
 
 
