@@ -322,3 +322,21 @@ class TextToVideoPipeline:
         if frames is None:                              # a frame-parallel rank other than 0: rank 0 has the clip
             return None
         return encode_mp4(frames, int(inp.get("fps", self.cfg.default_fps)))
+
+    def predict_many(self, inputs) -> list:
+        """A queue of hydrated inputs -> MP4 bytes in order; the MJPEG/MP4 encode of clip i (host, GIL released in the
+        native JPEG encoder) runs on a worker thread while the GPU denoises clip i+1."""
+        from concurrent.futures import ThreadPoolExecutor
+
+        from ...codecs.mp4 import encode_mp4
+        with ThreadPoolExecutor(max_workers=2) as pool:
+            futs = []
+            for inp in inputs:
+                frames = self.generate(prompt=inp["prompt"], negative_prompt=inp.get("negative_prompt", "") or "",
+                                       num_frames=inp.get("num_frames"),
+                                       num_inference_steps=int(inp.get("num_inference_steps", 50)),
+                                       width=inp.get("width"), height=inp.get("height"),
+                                       guidance_scale=inp.get("guidance_scale"), seed=int(inp.get("seed", 0)))
+                futs.append(None if frames is None else
+                            pool.submit(encode_mp4, frames, int(inp.get("fps", self.cfg.default_fps))))
+            return [None if f is None else f.result() for f in futs]

@@ -62,6 +62,11 @@ def test_eager_video_pipeline_cpu():
     assert a.shape == (4, 32, 32, 3) and a.dtype == np.uint8 and (a == b).all()
     mp4 = pipe.predict({"prompt": "x", "num_frames": 4, "num_inference_steps": 2, "width": 32, "height": 32, "fps": 8, "seed": 1})
     assert mp4[4:8] == b"ftyp" and len(demux_samples(mp4)) == 4
+    # the queue API gives the same bytes, in order
+    q = [{"prompt": "x", "num_frames": 4, "num_inference_steps": 2, "width": 32, "height": 32, "fps": 8, "seed": sd}
+         for sd in (1, 2, 1)]
+    many = pipe.predict_many(q)
+    assert many[0] == mp4 and many[2] == mp4 and many[1] != mp4
 
 
 def test_frame_split_rules():
