@@ -38,7 +38,7 @@ class CostModel:
     # ms per task measured on B200 at the template defaults (profiles/multigpu_n8_v1.md); the P=2 rows are
     # the guidance-parallel pair predictors and only count where such a predictor was actually built
     MEASURED_B200 = {"anythingv3": {1: 127.0, 2: 110.0}, "zeroscopev2xl": {1: 15000.0, 2: 7800.0},
-                     "kandinsky2": {1: 883.0, 2: 703.0}}
+                     "kandinsky2": {1: 883.0, 2: 703.0}, "damo": {1: 1135.0}}
 
     # ms per task of the frame-parallel text-to-video predictors (tests/mp_frame_parallel.py scaled to 50 steps)
     MEASURED_B200_FRAMES = {"zeroscopev2xl": {2: 7900.0, 4: 4566.0, 8: 2768.0}}   # profiles/multigpu_frame_parallel_v0.md
