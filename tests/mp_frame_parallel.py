@@ -54,9 +54,10 @@ def main():
     if full:
         del ref, par
         torch.cuda.empty_cache()
-        zcfg = TextToVideoConfig.zeroscope_xl()
+        fam = os.environ.get("AB_FP_MODEL", "zeroscopev2xl")              # or "damo" (256x256x16)
+        zcfg = TextToVideoConfig.zeroscope_xl() if fam == "zeroscopev2xl" else TextToVideoConfig.damo()
         zkw = dict(prompt="a panda eating bamboo on a rock", negative_prompt="noisy, washed out", num_inference_steps=4)
-        zref = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16)
+        zref = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16, family=fam)
         a = zref.generate(seed=3, **zkw)
 
         def vtime(p):
@@ -71,21 +72,22 @@ def main():
         t_ref = vtime(zref)
         del zref
         torch.cuda.empty_cache()
-        zpar = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16, frame_parallel=heap, **extra)
+        zpar = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16, family=fam, frame_parallel=heap,
+                                   **extra)
         b = zpar.generate(seed=3, **zkw)
         same = bool((a == b).all()) if rank == 0 else (b is None or both)
-        print(f"rank {rank} ZeroScope XL 1024x576x24 (4 steps) world={world} {layout} bit-identical={same}", flush=True)
+        print(f"rank {rank} {fam} default clip (4 steps) world={world} {layout} bit-identical={same}", flush=True)
         ok = ok and same
         t_par = vtime(zpar)
         if rank == 0:
-            print(f"RESULT zeroscope frame_parallel world={world} {layout} 4-step latency_ms={t_par:.1f} single_gpu_latency_ms={t_ref:.1f} "
+            print(f"RESULT {fam} frame_parallel world={world} {layout} 4-step latency_ms={t_par:.1f} single_gpu_latency_ms={t_ref:.1f} "
                   f"barriers_per_task={zpar._shard.barriers // 2}", flush=True)
         if os.environ.get("AB_FP_STEPS50", "0") == "1":        # the template's default task: 50 steps
             zkw["num_inference_steps"] = 50
             zpar.generate(seed=5, **zkw)                       # capture
             t50 = vtime(zpar)
             if rank == 0:
-                print(f"RESULT zeroscope frame_parallel world={world} {layout} 50-step task latency_ms={t50:.1f}", flush=True)
+                print(f"RESULT {fam} frame_parallel world={world} {layout} 50-step task latency_ms={t50:.1f}", flush=True)
     heap.close()
     if both:
         extra["cfg_parallel"].close()
