@@ -59,6 +59,9 @@ def main():
         zkw = dict(prompt="a panda eating bamboo on a rock", negative_prompt="noisy, washed out", num_inference_steps=4)
         zref = TextToVideoPipeline(zcfg, backend="native", device=dev, dtype=torch.float16, family=fam)
         a = zref.generate(seed=3, **zkw)
+        a2 = zref.generate(seed=3, **zkw)
+        if rank == 0:
+            print(f"single-GPU run-to-run identical: {bool((a == a2).all())}", flush=True)
 
         def vtime(p):
             torch.cuda.synchronize()
@@ -76,6 +79,10 @@ def main():
                                    **extra)
         b = zpar.generate(seed=3, **zkw)
         same = bool((a == b).all()) if rank == 0 else (b is None or both)
+        if rank == 0 and not same:
+            bad = (a != b).reshape(a.shape[0], -1).any(1)
+            print(f"frames that differ: {bad.nonzero()[0].tolist()} max diff {int(abs(a.astype(int) - b.astype(int)).max())} "
+                  f"pixels {int((a != b).sum())} of {a.size}", flush=True)
         print(f"rank {rank} {fam} default clip (4 steps) world={world} {layout} bit-identical={same}", flush=True)
         ok = ok and same
         t_par = vtime(zpar)
