@@ -50,6 +50,11 @@ class _TemporalConv:
         return y.view(b, f, h, w, c)
 
 
+import threading
+
+TemporalShardInfo = threading.local()      # .ranks: how many ranks the clip's frames are spread over in THIS thread's forward
+
+
 class _Block:
     """BasicTransformerBlock weights (attn1 self, attn2 cross or second self, GEGLU feed-forward)."""
 
@@ -105,7 +110,10 @@ class _SpatialTransformer:
         n = ops.layernorm(t, *B.ln2)
         q = ops.gemm(n, B.wq2).view(b, f * l, h, d)                              # frames of a sample share its text
         lk = kv.shape[1]
-        a = ops.flash_attn(q, kv[..., :c].view(b, lk, h, d), kv[..., c:].view(b, lk, h, d))
+        # a frame-sharded rank holds f/P of the sample's query rows: the kernel choice must be the whole clip's
+        ranks = getattr(TemporalShardInfo, "ranks", 1)
+        a = ops.flash_attn(q, kv[..., :c].view(b, lk, h, d), kv[..., c:].view(b, lk, h, d),
+                           long_queries=ranks > 1 and f * l * ranks > 128)
         t = ops.gemm(a.view(b * f * l, c), B.wo2, B.bo2, residual=t)
         t = B.feed_forward(t)
         return ops.gemm(t, self.pow, self.pob, residual=x.view(b * f * l, c)).view(b, f, hh, ww, c)
@@ -220,6 +228,7 @@ class NativeUNet3D:
 
     def set_frame_shard(self, shard) -> None:
         """Run the temporal layers across the ranks of ``shard`` (parallel/frame_shard.py); None: single GPU."""
+        self.frame_ranks = shard.world if shard is not None else 1
         mods = [self.transformer_in, self.mid["tatt"]] + self.mid["tc"]
         for blk in self.down + self.up:
             mods += blk["tc"] + (blk["tatt"] or [])
@@ -243,6 +252,7 @@ class NativeUNet3D:
         """x [B, F, H, W, 4] -> eps [B, F, H, W, 4]."""
         b, f, hh, ww, _ = x.shape
         it = iter(kvs)
+        TemporalShardInfo.ranks = getattr(self, "frame_ranks", 1)
         h = ops.conv_direct(x.view(b * f, hh, ww, -1), self.conv_in_w, self.conv_in_b).view(b, f, hh, ww, -1)
         h = self.transformer_in(h)
         skips = [h]

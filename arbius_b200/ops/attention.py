@@ -13,7 +13,9 @@ from .native import AttnArgs
 
 
 def flash_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, scale: Optional[float] = None,
-               causal: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+               causal: bool = False, out: Optional[torch.Tensor] = None, long_queries: bool = False) -> torch.Tensor:
+    """``long_queries``: choose the kernel as for more than 128 query rows per batch element even if this call has
+    fewer — for a rank that holds a slice of a longer query sequence, so the bytes do not depend on the split."""
     lib = native.load()
     b, lq, h, d = q.shape
     lk = k.shape[1]
@@ -29,7 +31,7 @@ def flash_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, scale: Opti
     a.v_bs, a.v_ls = v.stride(0), v.stride(1)
     a.o_bs, a.o_ls = out.stride(0), out.stride(1)
     a.scale = float(scale) if scale is not None else 0.0
-    a.causal = int(causal)
+    a.causal = int(causal) | (2 if long_queries else 0)
     a.dtype = native.dtype_code(q.dtype)
     native.check(lib.ab_flash_attn(C.byref(a), native.stream_ptr()), "ab_flash_attn")
     return out

@@ -312,7 +312,7 @@ extern "C" int ab_flash_attn(const ab_attn_args* a, void* stream_) {
     p.o_bs = a->o_bs; p.o_ls = a->o_ls;
     const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
     p.scale_log2 = scale * 1.4426950408889634f;
-    p.causal = a->causal;
+    p.causal = a->causal & 1;   // bit 1 of the field: choose the kernel as for a query length above 128 (see header)
     CUtensorMap tq, tk, tv;
     auto mk = [&](CUtensorMap* tm, const void* base, int L, long long bs, long long ls) {
         uint64_t dims[4] = {(uint64_t)D, (uint64_t)a->heads, (uint64_t)L, (uint64_t)a->batch};
@@ -324,7 +324,7 @@ extern "C" int ab_flash_attn(const ab_attn_args* a, void* stream_) {
     if (mk(&tk, a->k, a->lk, a->k_bs, a->k_ls)) return -1;
     if (mk(&tv, a->v, a->lk, a->v_bs, a->v_ls)) return -1;
 #define AB_ATT(T)                                                      \
-    (nch == 1 ? (a->lq > 128 ? launch_attn2<T>(tq, tk, tv, p, stream) : launch_attn<1, T>(tq, tk, tv, p, stream)) \
+    (nch == 1 ? ((a->lq > 128 || (a->causal & 2)) ? launch_attn2<T>(tq, tk, tv, p, stream) : launch_attn<1, T>(tq, tk, tv, p, stream)) \
      : nch == 2 ? launch_attn<2, T>(tq, tk, tv, p, stream)             \
                 : launch_attn<3, T>(tq, tk, tv, p, stream))
     return a->dtype == AB_BF16 ? AB_ATT(__nv_bfloat16) : AB_ATT(__half);

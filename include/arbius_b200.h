@@ -166,7 +166,9 @@ typedef struct {
   int batch, heads, lq, lk, head_dim;
   long long q_bs, q_ls, k_bs, k_ls, v_bs, v_ls, o_bs, o_ls;
   float scale;
-  int causal;
+  int causal;               /* bit 0: causal mask. bit 1: pick the kernel as for lq > 128 (two query tiles per CTA) even when
+                             * this call's lq is not: a rank that holds part of a longer query sequence (frames of a clip)
+                             * must run the kernel the whole sequence gets, the two kernels round differently */
   int dtype;
 } ab_attn_args;
 int ab_flash_attn(const ab_attn_args* args, void* stream);
