@@ -41,7 +41,7 @@ class CostModel:
                      "kandinsky2": {1: 883.0, 2: 703.0}, "damo": {1: 1135.0}}
 
     # ms per task of the frame-parallel text-to-video predictors (tests/mp_frame_parallel.py scaled to 50 steps)
-    MEASURED_B200_FRAMES = {"zeroscopev2xl": {2: 7900.0, 4: 4566.0, 8: 2768.0}}   # profiles/multigpu_frame_parallel_v0.md
+    MEASURED_B200_FRAMES = {"zeroscopev2xl": {2: 7900.0, 4: 4566.0, 8: 2768.0}, "damo": {2: 993.0}}   # profiles/multigpu_frame_parallel_v0.md
 
     @classmethod
     def measured_b200(cls, pair_families: Sequence[str] = (), frame_families: Sequence[str] = (),
