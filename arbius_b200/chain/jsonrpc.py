@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import itertools
 import json
+import threading
 import time
 import urllib.request
 from typing import Any, Callable, Dict, List, Optional, Sequence
@@ -69,6 +70,23 @@ class JsonRpcProvider:
         return bytes.fromhex(res[2:])
 
 
+# One lock and one local nonce counter per (provider, sender): the miner sends from several threads (one solve per GPU,
+# plus claims / stake / automine on the main thread) through several Contract objects that share a key. Reading
+# eth_getTransactionCount and sending must be atomic per sender, or two threads sign the same nonce and one
+# transaction — a finished solve's commitment, say — is rejected ("nonce too low" / "replacement underpriced").
+_sender_locks: Dict[tuple, threading.Lock] = {}
+_sender_nonce: Dict[tuple, int] = {}
+_sender_guard = threading.Lock()
+
+
+def _sender_lock(key: tuple) -> threading.Lock:
+    with _sender_guard:
+        lk = _sender_locks.get(key)
+        if lk is None:
+            lk = _sender_locks[key] = threading.Lock()
+        return lk
+
+
 class Contract:
     """address + function/event tables bound to a provider (and optionally a signing key)"""
 
@@ -93,12 +111,22 @@ class Contract:
         if self._chain_id is None:
             self._chain_id = self.p.chain_id()
         data = CA.encode_call(self.functions, name, args)
-        tx = Transaction(chain_id=self._chain_id, nonce=self.p.nonce(self.sender), to=self.address, data=data, gas=gas,
-                         gas_price=self.p.gas_price())
-        try:
-            txhash = self.p.request("eth_sendRawTransaction", ["0x" + sign_transaction(tx, self.key).hex()])
-        except JsonRpcError as e:
-            raise ChainError(decode_revert(e.data) or e.message) from e
+        skey = (id(self.p), self.sender)
+        with _sender_lock(skey):
+            for attempt in range(3):
+                nonce = max(self.p.nonce(self.sender), _sender_nonce.get(skey, 0))
+                tx = Transaction(chain_id=self._chain_id, nonce=nonce, to=self.address, data=data, gas=gas,
+                                 gas_price=self.p.gas_price())
+                try:
+                    txhash = self.p.request("eth_sendRawTransaction", ["0x" + sign_transaction(tx, self.key).hex()])
+                    _sender_nonce[skey] = nonce + 1
+                    break
+                except JsonRpcError as e:
+                    msg = (decode_revert(e.data) or e.message or "")
+                    if attempt < 2 and ("nonce" in msg.lower() or "underpriced" in msg.lower()):
+                        _sender_nonce.pop(skey, None)            # another process used this key: resynchronise
+                        continue
+                    raise ChainError(msg) from e
         if not wait:
             return {"transactionHash": txhash}
         deadline = time.time() + timeout

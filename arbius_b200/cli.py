@@ -377,7 +377,30 @@ def build_parser() -> argparse.ArgumentParser:
                 sp.add_argument(f"--{prm[0]}", help=prm[1], required=True)
     node = sub.add_parser("node", help="start the devchain JSON-RPC node (npx hardhat node stand-in)")
     node.add_argument("rest", nargs=argparse.REMAINDER)
+    gold = sub.add_parser("golden", help="boot self-test goldens: check them, or record them with --write "
+                                          "(miner/src/index.ts:983-1001 keeps one hard-coded CID; here one per "
+                                          "template, library build and GPU model)")
+    gold.add_argument("mining_config", help="MiningConfig.json of the miner")
+    gold.add_argument("--write", action="store_true", help="record the CIDs this box produces as the goldens")
     return ap
+
+
+def golden_main(a) -> int:
+    """Builds the miner exactly as ``python -m arbius_b200.miner`` would (same predictors, same IPFS strategy), runs
+    the fixed probe on every enabled model and compares with / writes the golden file."""
+    from .miner.node import FatalMinerError
+    from .miner.start import start
+    node = start(a.mining_config, run=False)
+    try:
+        got = node.boot_self_test(write=a.write)
+    except FatalMinerError:
+        print("golden mismatch: this box does not reproduce the recorded CIDs", file=sys.stderr)
+        return 1
+    for k, v in sorted(got.items()):
+        print(("wrote   " if a.write else "matches ") + f"{k}  {v}")
+    if not got:
+        print("no goldens recorded for this (template, library, GPU); run with --write on a verified box")
+    return 0
 
 
 def main(argv: Optional[List[str]] = None) -> int:
@@ -385,6 +408,8 @@ def main(argv: Optional[List[str]] = None) -> int:
     if a.task == "node":
         from .chain.rpc_server import main as node_main
         return node_main(a.rest)
+    if a.task == "golden":
+        return golden_main(a)
     try:
         env = Env(a)
         TASKS[a.task]["fn"](env, a)

@@ -41,11 +41,15 @@ class FatalMinerError(SystemExit):
     """Conditions on which the reference calls process.exit(1)."""
 
 
+def _reject_json_constant(name: str):
+    raise ValueError(f"{name} is not valid JSON")
+
+
 class MinerNode:
     def __init__(self, config: MiningConfig, chain: ChainClient, ml: MLBackend, models: Sequence[ModelEntry],
                  db: Optional[MinerDB] = None, n_gpus: int = 1, cost: Optional[CostModel] = None,
                  sleep: Callable[[float], None] = time.sleep, retry_sleep: Optional[Callable[[float], None]] = None,
-                 pin: bool = False, slots: int = 1):
+                 pin: bool = False, slots: int = 1, goldens=None, solve_retries: int = 2):
         self.c = config
         self.chain = chain
         self.ml = ml
@@ -55,6 +59,8 @@ class MinerNode:
         self._sleep = sleep
         self._retry_sleep = retry_sleep or sleep
         self.pin = pin
+        self.goldens = goldens                  # GoldenStore: when set, bootup() runs the determinism self-test
+        self.solve_retries = solve_retries      # automatic replays of a failed solve before it is dead-lettered
         self._inflight: Dict[int, Future] = {}
         self._lock = threading.RLock()
         self.solved: List[dict] = []            # per-task latency log (metrics)
@@ -84,8 +90,12 @@ class MinerNode:
         if raw is None:
             return False
         try:
-            pre = json.loads(raw.decode("utf-8"))
-        except (UnicodeDecodeError, json.JSONDecodeError):
+            # JSON.parse semantics (index.ts:160-164): NaN / Infinity are syntax errors, and indexing a non-object top
+            # level throws inside hydrateInput — both make the task invalid for every reference miner, so here too
+            pre = json.loads(raw.decode("utf-8"), parse_constant=_reject_json_constant)
+            if pre is None:
+                raise ValueError("null input")
+        except (UnicodeDecodeError, ValueError):
             log.warning("Task (%s) unable to parse input", taskid)
             self.db.store_invalid_task(taskid)
             return False
@@ -244,10 +254,20 @@ class MinerNode:
             return
         t_model = time.monotonic()
         commitment = generate_commitment(self.chain.address, taskid, cid)
-        try:
-            self.chain.signal_commitment(commitment)
-        except ChainError as e:
-            log.error("Commitment submission failed %s", e)
+
+        def commit():
+            try:
+                self.chain.signal_commitment(commitment)
+                return True
+            except ChainError as e:
+                if "nonce" in str(e).lower() or "underpriced" in str(e).lower():
+                    raise                       # a sender race, not a protocol answer: retry, the GPU work is done
+                log.error("Commitment submission failed %s", e)
+                return False
+        ok = self._retry(commit, 5, 1.25)
+        if ok is None:
+            raise RuntimeError(f"signalCommitment for {taskid} kept failing; the solve is kept for replay")
+        if not ok:
             return
 
         def submit():
@@ -338,7 +358,15 @@ class MinerNode:
             if isinstance(err, FatalMinerError):
                 raise err
             log.error("Job (%s) [%s] failed: %s", job.id, job.method, err)
-            self.db.store_failed_job(job)
+            d = job.decoded()
+            tries = int(d.get("_retries", 0))
+            if job.method == "solve" and tries < self.solve_retries:
+                # the reference dead-letters and forgets (index.ts:935-937); a solve is worth a bounded replay
+                d["_retries"] = tries + 1
+                self.db.queue_job("solve", priority=job.priority, waituntil=self.chain.now() + 5 * (tries + 1),
+                                  concurrent=False, data=d)
+            else:
+                self.db.store_failed_job(job)
         self.db.delete_job(job.id)
         with self._lock:
             self._inflight.pop(job.id, None)
@@ -389,10 +417,36 @@ class MinerNode:
             raise FatalMinerError(1)
         return cid
 
+    def boot_self_test(self, write: bool = False) -> Dict[str, str]:
+        """index.ts:983-1001 for every enabled model: the fixed probe must hash to the golden recorded for this
+        (template, library build, GPU model). A mismatch is fatal; a model without a golden is recorded when
+        ``write`` (the ``golden --write`` CLI task) and reported otherwise."""
+        from .golden import environment_key, selftest_input
+        out: Dict[str, str] = {}
+        if self.goldens is None or self.c.evilmode:
+            return out
+        for m in self.models:
+            if not m.mineable:
+                continue
+            key = environment_key(m.name or m.id)
+            expected = None if write else self.goldens.get(key)
+            if expected is None and not write:
+                log.warning("self-test: no golden CID recorded for %s — run `golden --write` on a verified box", key)
+                continue
+            cid = self.self_test(m, selftest_input(m.template), expected)
+            if cid is None:
+                log.error("self-test: model %s produced no CID", key)
+                raise FatalMinerError(1)
+            if write:
+                self.goldens.put(key, cid)
+            out[key] = cid
+        return out
+
     def bootup(self) -> None:
         self.db.clear_jobs_by_method("validatorStake")
         self.db.clear_jobs_by_method("automine")
         self.version_check()
+        self.boot_self_test()
         self.db.queue_job("validatorStake", priority=30, waituntil=0, concurrent=False, data={})
         if self.c.automine.enabled:
             self.db.queue_job("automine", priority=5, waituntil=0, concurrent=False, data={})

@@ -130,8 +130,9 @@ def start(config_path: str, run: bool = True) -> MinerNode:
     ml = make_backend(c, predictors, subset_predictors, slots)
     n_gpus = c.scheduler.gpus or max([ml.endpoints(m) for m in models] + [1])
     n_gpus = max(p for p in (1, 2, 4, 8) if p <= n_gpus)
+    from .golden import GoldenStore, default_path
     node = MinerNode(c, chain, ml, models, db=db, n_gpus=n_gpus, cost=cost, pin=c.ipfs.strategy != "local",
-                     slots=slots)
+                     slots=slots, goldens=GoldenStore(default_path(c)))
     initialize_rpc(db, c.rpc.host, c.rpc.port, node)
     if run:
         node.run_forever()

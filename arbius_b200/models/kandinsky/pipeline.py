@@ -182,11 +182,8 @@ class Kandinsky2Pipeline:
         import sys
         heap, r, par = self.cfgp, self.cfgp.rank, i & 1
         gemm_mod = sys.modules["arbius_b200.ops.gemm"]
-        gemm_mod.BATCH_SCALE = 2                      # split-K choices of the undivided batch of two
-        try:
+        with gemm_mod.batch_scale(2):                 # split-K choices of the undivided batch of two
             e = self.unet.forward(st["xin"][r:r + 1], emb_all[r:r + 1], sample_offset=r)
-        finally:
-            gemm_mod.BATCH_SCALE = 1
         slot = st["ex"][par]
         slot.copy_(e)
         heap.barrier_replayable()

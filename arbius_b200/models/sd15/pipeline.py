@@ -153,18 +153,13 @@ class SD15Pipeline:
     def _run_native(self, st: dict, sch: Scheduler, g: float) -> None:
         """Everything between 'ids are on the device' and 'uint8 pixels are on the device', for the ``nb`` tasks of this
         state at once (UNet batch = [nb negative prompts, nb prompts]). Every split-K choice is the one a lone task
-        gets (``BATCH_SCALE``), all other kernels are per-sample, so a task's bytes do not depend on its batch mates."""
+        gets (``ops.gemm.batch_scale``, per thread), all other kernels are per-sample, so a task's bytes do not depend on its batch mates."""
         import sys
         from fractions import Fraction
         gemm_mod = sys.modules["arbius_b200.ops.gemm"]
         nb = st["nb"]
-        if nb > 1:
-            gemm_mod.BATCH_SCALE = Fraction(1, nb)
-        try:
+        with gemm_mod.batch_scale(Fraction(1, nb) if nb > 1 else 1):
             self._run_native_body(st, sch, g, nb)
-        finally:
-            if nb > 1:
-                gemm_mod.BATCH_SCALE = 1
 
     def _run_native_body(self, st: dict, sch: Scheduler, g: float, nb: int) -> None:
         ctx = self.clip.forward(st["ids"])
@@ -196,11 +191,8 @@ class SD15Pipeline:
         import sys
         heap, r, par = self.cfgp, self.cfgp.rank, i & 1
         gemm_mod = sys.modules["arbius_b200.ops.gemm"]
-        gemm_mod.BATCH_SCALE = 2                      # tile/split-K choices of the undivided batch of two
-        try:
+        with gemm_mod.batch_scale(2):                 # tile/split-K choices of the undivided batch of two
             e = self.unet.forward(st["xin"][r:r + 1], temb[2 * i + r:2 * i + r + 1], [kv[r:r + 1] for kv in kvs])
-        finally:
-            gemm_mod.BATCH_SCALE = 1
         slot = st["ex"][par]
         slot.copy_(e)
         heap.barrier_replayable()

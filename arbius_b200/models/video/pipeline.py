@@ -172,11 +172,8 @@ class TextToVideoPipeline:
             for b in range(2):
                 ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=sch.input_scale(i))
             if self.cfgp is None:
-                gemm_mod.BATCH_SCALE = P               # every UNet GEMM's rows scale with the frames: canonical = all
-                try:
+                with gemm_mod.batch_scale(P):          # every UNet GEMM's rows scale with the frames: canonical = all
                     e = self.unet.forward(st["xin"], temb[2 * nf * i:2 * nf * (i + 1)], kvs)
-                finally:
-                    gemm_mod.BATCH_SCALE = 1
                 ops.cfg_step(e[1], e[0], None, g=g, eps_out=f["eps"])
             else:
                 self._cfg_parallel_step(st, i, temb, kvs, g)
@@ -188,12 +185,9 @@ class TextToVideoPipeline:
         vscale = 1
         if P > 1 and chunk % P == 0:
             chunk, vscale = chunk // P, P              # the single-GPU chunk, cut over the ranks
-        gemm_mod.BATCH_SCALE = vscale
-        try:
+        with gemm_mod.batch_scale(vscale):
             for i in range(0, nf, chunk):
                 chunks.append(ops.finalize_u8(self.vae.forward(st["lat"][0, i:i + chunk])))
-        finally:
-            gemm_mod.BATCH_SCALE = 1
         st["u8"] = torch.cat(chunks, 0) if len(chunks) > 1 else chunks[0]
         if self.fp is not None:
             # every rank stores its frames into rank 0's clip buffer, then all meet: rank 0 owns the whole clip
@@ -211,12 +205,9 @@ class TextToVideoPipeline:
         import sys
         heap, r, par, nf = self.cfgp, self.cfgp.rank, i & 1, st["nfl"]
         gemm_mod = sys.modules["arbius_b200.ops.gemm"]
-        gemm_mod.BATCH_SCALE = 2 * (self.fp.world if self.fp is not None else 1)
-        try:
+        with gemm_mod.batch_scale(2 * (self.fp.world if self.fp is not None else 1)):
             rows = temb[2 * nf * i + r * nf:2 * nf * i + (r + 1) * nf]
             e = self.unet.forward(st["xin"][r:r + 1], rows, [kv[r:r + 1] for kv in kvs])
-        finally:
-            gemm_mod.BATCH_SCALE = 1
         slot = st["ex"][par]
         slot.copy_(e)
         heap.barrier_replayable()

@@ -9,8 +9,10 @@ Weights arrive in their upstream layout (``nn.Linear`` [N, K], ``nn.Conv2d``
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import json
+import threading
 from pathlib import Path
 from typing import Optional
 
@@ -30,11 +32,28 @@ RECORD: Optional[list] = None      # set to a list to log every (key, call kwarg
 # runs one of the two UNet branches) every tiling decision that changes the summation order (split-K) must be the one
 # the undivided batch would get, or the bytes would depend on the GPU count. The models set this around their calls.
 # A Fraction 1/n is set while n independent tasks share one batch: each task then gets the choices it gets alone.
-BATCH_SCALE = 1
+# The multiplier is per host thread: the miner drives one thread per GPU in one process, and a thread that warms up a
+# pair / frame / batched predictor must not change the split-K another thread bakes into the graph it is capturing.
+_scale_tls = threading.local()
+
+
+def get_batch_scale():
+    return getattr(_scale_tls, "value", 1)
+
+
+@contextlib.contextmanager
+def batch_scale(value):
+    """``with batch_scale(v):`` — the canonical-batch multiplier for the GEMM/conv calls of THIS thread."""
+    prev = get_batch_scale()
+    _scale_tls.value = value
+    try:
+        yield
+    finally:
+        _scale_tls.value = prev
 
 
 def _canon(m: int) -> int:
-    return int(m * BATCH_SCALE)
+    return int(m * get_batch_scale())
 
 
 def _tuned_pair(key: str, actual_key: str):
@@ -42,7 +61,7 @@ def _tuned_pair(key: str, actual_key: str):
     canonical shape's entry; the tile width is free, so a batch of several tasks takes the entry of its real shape if
     there is one and otherwise lets the library size the tile for the rows it really has (block_n 0)."""
     cfg = tuned_config(key)
-    if cfg is None or BATCH_SCALE >= 1 or key == actual_key or _BATCH_BN == "canon":
+    if cfg is None or get_batch_scale() >= 1 or key == actual_key or _BATCH_BN == "canon":
         return cfg
     own = tuned_config(actual_key)
     if own is None and _BATCH_BN == "small" and cfg[0] > 96:
@@ -62,14 +81,23 @@ def tuned_config(key: str):
     return _tuned.get(key)
 
 
+_retired_workspaces: list = []
+_ws_lock = threading.Lock()
+
+
 def _workspace(nbytes: int, device) -> torch.Tensor:
-    """Per-device split-K scratch, grown on demand (never shrinks, reused stream-ordered)."""
+    """Per-device split-K scratch, grown on demand (never shrinks, reused stream-ordered). A buffer that is outgrown is
+    kept alive for the life of the process: CUDA graphs captured earlier hold its raw address, and freeing it would let
+    their replays write fp32 partials into memory the allocator has handed to another tensor."""
     key = (device.index if device.index is not None else torch.cuda.current_device())
-    ws = _workspaces.get(key)
-    if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(max(nbytes, 1 << 24), dtype=torch.uint8, device=device)
-        _workspaces[key] = ws
-    return ws
+    with _ws_lock:
+        ws = _workspaces.get(key)
+        if ws is None or ws.numel() < nbytes:
+            if ws is not None:
+                _retired_workspaces.append(ws)
+            ws = torch.empty(max(nbytes, 1 << 26), dtype=torch.uint8, device=device)
+            _workspaces[key] = ws
+        return ws
 
 
 def pack_conv_weight(w: torch.Tensor) -> torch.Tensor:
@@ -162,7 +190,7 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
             splitk: int = 0, block_n: int = 0, halo: bool = False) -> torch.Tensor:
     """3x3 / pad 1 / stride 1 implicit-GEMM conv. x [B,H,W,C1] (+ x2 [B,H,W,C2]), w_packed [Cout, 9*(C1+C2)].
     ``halo``: x (and x2) are [B, H + 2, W, C] — a row band of the image with the neighbouring bands' edge rows (or zeros
-    at the image's top and bottom) in rows 0 and H+1, as a patch-parallel rank holds it; ``BATCH_SCALE`` then counts
+    at the image's top and bottom) in rows 0 and H+1, as a patch-parallel rank holds it; ``batch_scale`` then counts
     the bands, so the split-K choice is the whole image's."""
     lib = native.load()
     b, h, wd, c1 = x.shape
@@ -225,7 +253,7 @@ def conv_temporal(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.
     Same implicit-GEMM kernel as conv3x3 with a 3x1 tap pattern over the (F, HW) "image".
     ``halo``: x is [B, F + 2, HW, C] — the local frames of a frame-sharded clip with the neighbours' frames (or zeros at
     the clip's ends) in rows 0 and F+1; ``frame_ranks`` is the number of ranks the frames are spread over
-    (default: ``BATCH_SCALE``, which may also carry a guidance-branch split of the batch)."""
+    (default: ``batch_scale``, which may also carry a guidance-branch split of the batch)."""
     lib = native.load()
     b, f, hw, c = x.shape
     if halo:
@@ -242,7 +270,7 @@ def conv_temporal(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.
     a.act, a.out_scale = ACT[act], 1.0
     a.dtype = native.dtype_code(x.dtype)
     if halo:
-        fr = frame_ranks or int(BATCH_SCALE)
+        fr = frame_ranks or int(get_batch_scale())
         key = f"tconv:{_canon(b) // fr}x{f * fr}x{hw}:{n}:{c}"
     else:
         key = f"tconv:{_canon(b)}x{f}x{hw}:{n}:{c}"

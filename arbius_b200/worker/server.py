@@ -33,9 +33,28 @@ def handle_prediction(predict: Predictor, template: dict, body: dict) -> dict:
     return encode_cog_output(data, output_mime(template))
 
 
-def make_server(predict: Predictor, template: dict, host: str, port: int) -> ThreadingHTTPServer:
+def is_fatal_device_error(e: BaseException) -> bool:
+    """A CUDA fault is sticky: the context is gone and every later prediction would fail the same way. The worker must
+    die (non-zero) so its supervisor restarts it, instead of answering 422 for ever."""
+    text = f"{type(e).__name__}: {e}".lower()
+    if type(e).__name__ in ("AcceleratorError", "OutOfMemoryError"):
+        return "out of memory" not in text           # OOM is recoverable; other accelerator errors are not
+    return any(s in text for s in ("cuda error", "cudaerror", "device-side assert", "illegal memory access",
+                                   "unspecified launch failure", "an illegal instruction", "launch failed",
+                                   "misaligned address"))
+
+
+def make_server(predict: Predictor, template: dict, host: str, port: int,
+                on_fatal: Callable[[BaseException], None] = None) -> ThreadingHTTPServer:
     lock = threading.Lock()       # one prediction at a time per GPU subset
     stats = {"served": 0, "ms": 0.0}
+
+    def die(e):
+        import os
+        import sys
+        print(f"arbius_b200 worker: fatal device error, exiting for restart: {e}", file=sys.stderr, flush=True)
+        os._exit(70)
+    fatal = on_fatal or die
 
     class H(BaseHTTPRequestHandler):
         def log_message(self, *a):
@@ -67,6 +86,10 @@ def make_server(predict: Predictor, template: dict, host: str, port: int) -> Thr
                 stats["ms"] = (time.monotonic() - t0) * 1e3
                 self._json(200, {"status": "succeeded", **out})
             except Exception as e:  # noqa: BLE001
+                if is_fatal_device_error(e):
+                    self._json(500, {"status": "failed", "detail": str(e), "fatal": True})
+                    fatal(e)
+                    return
                 self._json(422, {"status": "failed", "detail": str(e)})
 
     return ThreadingHTTPServer((host, port), H)

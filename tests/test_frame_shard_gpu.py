@@ -62,16 +62,13 @@ def test_halo_temporal_conv_matches_undivided_bytes(world):
     ref = ops.conv_temporal(x, w, bias, residual=res)
     fl = f // world
     zero = torch.zeros(b, 1, hw, c, dtype=x.dtype, device="cuda")
-    gemm_mod.BATCH_SCALE = world
-    try:
+    with gemm_mod.batch_scale(world):
         for r in range(world):
             prev = x[:, r * fl - 1:r * fl] if r > 0 else zero
             nxt = x[:, (r + 1) * fl:(r + 1) * fl + 1] if r < world - 1 else zero
             pad = torch.cat([prev, x[:, r * fl:(r + 1) * fl], nxt], 1).contiguous()
             got = ops.conv_temporal(pad, w, bias, residual=res[:, r * fl:(r + 1) * fl].contiguous(), halo=True)
             assert torch.equal(got, ref[:, r * fl:(r + 1) * fl]), f"rank {r}"
-    finally:
-        gemm_mod.BATCH_SCALE = 1
 
 
 @pytest.mark.parametrize("world,frames", [(2, 24), (4, 24), (8, 24), (2, 8), (2, 16)])
@@ -135,10 +132,7 @@ def test_halo_conv3x3_row_bands_match_undivided_bytes(world, concat):
         top = t[:, r * hl - 1:r * hl] if r > 0 else z
         bot = t[:, (r + 1) * hl:(r + 1) * hl + 1] if r < world - 1 else z
         return torch.cat([top, t[:, r * hl:(r + 1) * hl], bot], 1).contiguous()
-    gemm_mod.BATCH_SCALE = world
-    try:
+    with gemm_mod.batch_scale(world):
         for r in range(world):
             got = ops.conv3x3(band(x, r), w, bias, x2=band(x2, r) if concat else None, act="silu", halo=True)
             assert torch.equal(got, ref[:, r * hl:(r + 1) * hl]), f"rank {r}"
-    finally:
-        gemm_mod.BATCH_SCALE = 1

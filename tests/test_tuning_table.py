@@ -13,18 +13,16 @@ G = sys.modules["arbius_b200.ops.gemm"]
 def test_split_k_always_comes_from_the_canonical_shape():
     table = json.loads(Path(G.__file__).with_name("tuned_sm100.json").read_text())
     assert table["conv:2x8x8:1280:1280"][1] > 1                     # a split-K shape of the lone task
-    try:
-        for n in (2, 4, 8):
-            G.BATCH_SCALE = Fraction(1, n)
+    for n in (2, 4, 8):
+        with G.batch_scale(Fraction(1, n)):
             assert G._canon(2 * n) == 2
             bn, sk = G._tuned_pair("conv:2x8x8:1280:1280", f"conv:{2 * n}x8x8:1280:1280")
             assert sk == table["conv:2x8x8:1280:1280"][1]
             own = table.get(f"conv:{2 * n}x8x8:1280:1280")
             assert bn == (own[0] if own else 0)                      # real shape's tile width, or the library's choice
-        G.BATCH_SCALE = 2                                            # guidance / frame split: canonical entry as is
+    with G.batch_scale(2):                                           # guidance / frame split: canonical entry as is
         assert G._tuned_pair("conv:2x8x8:1280:1280", "conv:1x8x8:1280:1280") == table["conv:2x8x8:1280:1280"]
-    finally:
-        G.BATCH_SCALE = 1
+    assert G.get_batch_scale() == 1
     assert G._tuned_pair("conv:2x8x8:1280:1280", "conv:2x8x8:1280:1280") == table["conv:2x8x8:1280:1280"]
     assert G._tuned_pair("conv:3x5x7:64:64", "conv:3x5x7:64:64") is None
 
