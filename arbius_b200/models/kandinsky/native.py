@@ -144,6 +144,95 @@ class _KRes:
         sc = ops.gemm(x, self.sw, self.sb, x2=x2) if self.sw is not None else x
         return ops.conv3x3(h, self.c2w, self.c2b, residual=sc)
 
+    # ---- patch parallelism (parallel/patch.py): x is this rank's row band of a sharded level -------------------
+    def patch(self, ctx, x: torch.Tensor, emb_all: torch.Tensor, x2: Optional[torch.Tensor], sharded: bool):
+        """Returns (out, out_sharded). ``sharded``: x (and x2) are [B, H/P, W, C] row bands; otherwise full tensors of a
+        replicated level. A level that does not split (``patch.shardable``) is gathered on the way down and computed
+        whole on every rank; on the way up every rank cuts its band (and halo rows) out of the whole tensor."""
+        from ...parallel import patch as pp
+        P, rk = ctx.world, ctx.rank
+        scale_of = ops.batch_scale
+        ss = emb_all[:, self.emb_off:self.emb_off + 2 * self.cout]
+        sc_, sh_ = ss[:, :self.cout], ss[:, self.cout:]
+        b = x.shape[0]
+        cin = x.shape[-1] + (x2.shape[-1] if x2 is not None else 0)
+        # hand-off state (buffers, flag sites) per input shape: allocated on first use, in the same order on every rank
+        st = self.__dict__.setdefault("_pp", {}).setdefault((tuple(x.shape), sharded), {})
+        if not sharded:
+            if not self.up or not pp.shardable(2 * x.shape[1], 2 * x.shape[2]):
+                with scale_of(1):
+                    return self(x, emb_all, x2=x2), False
+            # replicated level -> sharded level: resample whole, then cut this rank's band with its halo rows
+            assert x2 is None
+            with scale_of(1):
+                hf = ops.upsample_nearest2x(ops.groupnorm(x, *self.n1, self.groups, 1e-5, "silu"))
+                xf = ops.upsample_nearest2x(x)
+            H, W = hf.shape[1], hf.shape[2]
+            hl = H // P
+            key = ("cut", b, hl, W, cin)
+            if key not in st:
+                st[key] = torch.zeros((b, hl + 2, W, cin), dtype=x.dtype, device=x.device)
+            hb = st[key]
+            lo, hi = max(rk * hl - 1, 0), min((rk + 1) * hl + 1, H)
+            hb[:, lo - (rk * hl - 1):lo - (rk * hl - 1) + (hi - lo)].copy_(hf[:, lo:hi])
+            xb = xf[:, rk * hl:(rk + 1) * hl].contiguous()
+            with scale_of(P):
+                h = ops.conv3x3(hb, self.c1w, self.c1b, halo=True)
+                return self._patch_tail(ctx, st, h, xb, None, sc_, sh_), True
+        hl, W = x.shape[1], x.shape[2]
+        if self.down:
+            assert x2 is None
+            g1 = st.get("g1") or st.setdefault("g1", pp.PatchGroupNorm(ctx, b, hl, W, cin, self.groups, halo=False))
+            y = g1(x, *self.n1, 1e-5, "silu")
+            if hl % 2 == 0 and pp.shardable(hl * P // 2, W // 2):
+                he = st.get("he") or st.setdefault("he", pp.HaloExchange(ctx, b, hl // 2, W // 2, cin))
+                for i in range(b):
+                    extra.avgpool2x(y[i:i + 1], out=he.interior(i).unsqueeze(0))
+                he.push()
+                xb = extra.avgpool2x(x)
+                with scale_of(P):
+                    h = ops.conv3x3(he.buf, self.c1w, self.c1b, halo=True, sync=ctx.conv_sync(he.site))
+                    return self._patch_tail(ctx, st, h, xb, None, sc_, sh_), True
+            # the level below does not split: gather the whole tensors on every rank and go on as one GPU would
+            H = hl * P
+            gy = st.get("gy") or st.setdefault("gy", pp.BandGather(ctx, b, H, W, cin))
+            gx = st.get("gx") or st.setdefault("gx", pp.BandGather(ctx, b, H, W, cin))
+            gy.push(y)
+            gx.push(x)
+            yf, xf = gy.full(), gx.full()
+            with scale_of(1):
+                h, xx = extra.avgpool2x(yf), extra.avgpool2x(xf)
+                h = ops.conv3x3(h, self.c1w, self.c1b)
+                h = ops.groupnorm(h, *self.n2, self.groups, 1e-5, "silu", scale=sc_, shift=sh_)
+                sc = ops.gemm(xx, self.sw, self.sb) if self.sw is not None else xx
+                return ops.conv3x3(h, self.c2w, self.c2b, residual=sc), False
+        if self.up:
+            assert x2 is None
+            g1 = st.get("g1") or st.setdefault("g1", pp.PatchGroupNorm(ctx, b, hl, W, cin, self.groups, halo=False))
+            y = g1(x, *self.n1, 1e-5, "silu")
+            he = st.get("he") or st.setdefault("he", pp.HaloExchange(ctx, b, 2 * hl, 2 * W, cin))
+            for i in range(b):
+                ops.upsample_nearest2x(y[i:i + 1], out=he.interior(i).unsqueeze(0))
+            he.push()
+            xb = ops.upsample_nearest2x(x)
+            with scale_of(P):
+                h = ops.conv3x3(he.buf, self.c1w, self.c1b, halo=True, sync=ctx.conv_sync(he.site))
+                return self._patch_tail(ctx, st, h, xb, None, sc_, sh_), True
+        g1 = st.get("g1") or st.setdefault("g1", pp.PatchGroupNorm(ctx, b, hl, W, cin, self.groups, halo=True))
+        yb = g1(x, *self.n1, 1e-5, "silu", x2=x2)
+        with scale_of(P):
+            h = ops.conv3x3(yb, self.c1w, self.c1b, halo=True, sync=ctx.conv_sync(g1.done))
+            return self._patch_tail(ctx, st, h, x, x2, sc_, sh_), True
+
+    def _patch_tail(self, ctx, st, h, x, x2, sc_, sh_):
+        """norm2 (scale-shift) -> conv2 (+ skip) on row bands; runs under ``batch_scale(P)``."""
+        from ...parallel import patch as pp
+        b, hl, W, _ = h.shape
+        g2 = st.get("g2") or st.setdefault("g2", pp.PatchGroupNorm(ctx, b, hl, W, self.cout, self.groups, halo=True))
+        yb = g2(h, *self.n2, 1e-5, "silu", scale=sc_, shift=sh_)
+        sc = ops.gemm(x, self.sw, self.sb, x2=x2) if self.sw is not None else x
+        return ops.conv3x3(yb, self.c2w, self.c2b, residual=sc, halo=True, sync=ctx.conv_sync(g2.done))
+
 
 class _KAttn:
     def __init__(self, sd: SD, p: str, dtype, device, heads: int, groups: int):
@@ -157,28 +246,63 @@ class _KAttn:
         self.buf: Optional[torch.Tensor] = None
 
     def prepare(self, enc: torch.Tensor, l: int) -> None:
-        """enc [B, T, mc]: project the encoder tokens once per task into rows [0, T) of the K/V columns."""
+        """enc [B, T, mc]: project the encoder tokens once per task into the K/V columns of a [B, T, 3C] prefix buffer.
+        Keys are attended in the order [prefix | pixels] with the prefix in KV tiles of its own and the pixel tiles
+        counted from pixel 0 (csrc/attention_v2.cuh SegMaps) — at every GPU count, one included, so that a row-band
+        split of the pixels never changes a tile's contents."""
         b, t, _ = enc.shape
         c = self.c
-        self.buf = torch.zeros((b, t + l, 3 * c), dtype=enc.dtype, device=enc.device)
+        self.enc_kv = torch.zeros((b, t, 3 * c), dtype=enc.dtype, device=enc.device)
         self.t = t
         for i in range(b):
-            ops.gemm(enc[i], self.wekv, self.bekv, out=self.buf[i, :t, c:], splitk=1)
+            ops.gemm(enc[i], self.wekv, self.bekv, out=self.enc_kv[i, :, c:], splitk=1)
+        self.pix = torch.empty((b, l, 3 * c), dtype=enc.dtype, device=enc.device)
 
     off = 0                                    # first sample of the batch held here (guidance parallelism: the rank)
 
     def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        from ...parallel.patch import flash_attn_segs
         b, hh, ww, c = x.shape
         l, h, t = hh * ww, self.heads, self.t
-        n = ops.groupnorm(x, *self.norm, self.groups, 1e-5, None).view(b, l, c)
-        buf = self.buf[self.off:self.off + b]
-        for i in range(b):
-            ops.gemm(n[i], self.wqkv, self.bqkv, out=buf[i, t:], splitk=1)
-        q = buf[:, t:, :c].view(b, l, h, c // h)
-        k = buf[:, :, c:2 * c].view(b, t + l, h, c // h)
-        v = buf[:, :, 2 * c:].view(b, t + l, h, c // h)
-        a = ops.flash_attn(q, k, v)
+        d = c // h
+        n = ops.groupnorm(x, *self.norm, self.groups, 1e-5, None).view(b * l, c)
+        pix = self.pix[self.off:self.off + b]
+        ops.gemm(n, self.wqkv, self.bqkv, out=pix.view(b * l, 3 * c), splitk=1)
+        q = pix[:, :, :c].view(b, l, h, d)
+        a = flash_attn_segs(q, self.enc_kv[self.off:self.off + b].view(b, t, 3 * h, d), [pix.data_ptr()], l, 3 * c,
+                            l * 3 * c, h, d, k_head0=h, v_head0=2 * h, heads_total=3 * h, prefix_k_head0=h,
+                            prefix_v_head0=2 * h)
         return ops.gemm(a.view(b * l, c), self.wo, self.bo, residual=x.view(b * l, c)).view(b, hh, ww, c)
+
+    def patch(self, ctx, x: torch.Tensor, sharded: bool):
+        """Row-band form: the band's fused QKV projection lands in the peer heap, a flag follows it, and the attention
+        kernel fetches every KV tile from the GPU that owns it (waiting for that GPU's flag before its first load)."""
+        from ...parallel import patch as pp
+        if not sharded:
+            with ops.batch_scale(1):
+                return self(x), False
+        P, rk = ctx.world, ctx.rank
+        b, hl, ww, c = x.shape
+        ll, h, t = hl * ww, self.heads, self.t
+        d = c // h
+        st = self.__dict__.setdefault("_pp", {}).setdefault(tuple(x.shape), {})
+        if "gn" not in st:
+            st["gn"] = pp.PatchGroupNorm(ctx, b, hl, ww, c, self.groups, halo=False)
+            st["pix"], st["pix_off"] = ctx.heap.alloc((b, ll, 3 * c), x.dtype)
+            st["site"] = ctx.site()
+        n = st["gn"](x, *self.norm, 1e-5, None).view(b * ll, c)
+        pix = st["pix"]
+        with ops.batch_scale(P):
+            ops.gemm(n, self.wqkv, self.bqkv, out=pix.view(b * ll, 3 * c), splitk=1)
+            ctx.signal(st["site"])
+            q = pix[:, :, :c].view(b, ll, h, d)
+            srcs = [ctx.heap.peer_ptr(r, st["pix_off"]) for r in range(P)]
+            a = pp.flash_attn_segs(q, self.enc_kv[self.off:self.off + b].view(b, t, 3 * h, d), srcs, ll, 3 * c,
+                                   ll * 3 * c, h, d, k_head0=h, v_head0=2 * h, heads_total=3 * h, prefix_k_head0=h,
+                                   prefix_v_head0=2 * h, self_rank=rk,
+                                   sync=None if ctx.dry else (ctx.tick_ptr, st["site"].local))
+            out = ops.gemm(a.view(b * ll, c), self.wo, self.bo, residual=x.view(b * ll, c)).view(b, hl, ww, c)
+        return out, True
 
 
 class NativeKandinskyUNet:
@@ -307,6 +431,57 @@ class NativeKandinskyUNet:
             h = self._run(blk, h, emb_all, x2=hs.pop())
         h = ops.groupnorm(h, *self.out_norm, self.cfg.groups, 1e-5, "silu")
         return ops.conv_direct(h, *self.out_conv)
+
+
+    # ---- patch parallelism: one image's row bands on the GPUs of ``ctx`` (parallel/patch.py) ----------------------
+    def forward_patch(self, ctx, x: torch.Tensor, emb_all: torch.Tensor, sample_offset: int = 0) -> torch.Tensor:
+        """Same contract as ``forward`` (whole x in, whole prediction out, on every rank), computed with the sharded
+        levels split into row bands over ``ctx``'s GPUs. Bytes equal ``forward``'s."""
+        from ...parallel import patch as pp
+        P, rk = ctx.world, ctx.rank
+        for a in self.attn:
+            a.off = sample_offset
+        b, H, W, _ = x.shape
+        assert pp.shardable(H, W) and H % P == 0, f"latent {H}x{W} does not split into 8 canonical row bands"
+        st = self.__dict__.setdefault("_pp", {})
+        ctx.tick()
+        with ops.batch_scale(1):
+            hfull = ops.conv_direct(x, *self.conv_in)
+        hl = H // P
+        h = hfull[:, rk * hl:(rk + 1) * hl].contiguous()
+        sharded = True
+        hs = [(h, True)]
+
+        def run(layers, h, sharded, x2=None):
+            for m in layers:
+                if isinstance(m, _KRes):
+                    h, sharded = m.patch(ctx, h, emb_all, x2, sharded)
+                    x2 = None
+                else:
+                    h, sharded = m.patch(ctx, h, sharded)
+            return h, sharded
+        for blk in self.input_blocks:
+            h, sharded = run(blk, h, sharded)
+            hs.append((h, sharded))
+        h, sharded = run(self.middle, h, sharded)
+        for blk in self.output_blocks:
+            skip, skip_sharded = hs.pop()
+            assert skip_sharded == sharded, "skip connection and activation must live on the same kind of level"
+            h, sharded = run(blk, h, sharded, x2=skip)
+        assert sharded
+        c = h.shape[-1]
+        key = ("out", b, hl, W, c)
+        if key not in st:
+            st[key] = (pp.PatchGroupNorm(ctx, b, hl, W, c, self.cfg.groups, halo=True),
+                       pp.BandGather(ctx, b, H, W, self.out_conv[0].cout))
+        gno, gat = st[key]
+        yb = gno(h, *self.out_norm, 1e-5, "silu")
+        ctx.wait(gno.done, ctx.nb_mask)
+        with ops.batch_scale(1):
+            e = ops.conv_direct(yb, *self.out_conv)                      # [B, hl+2, W, out]: rows 1..hl are the band
+        row_b = W * e.shape[-1] * e.element_size()
+        gat.push(None, src_batch_pitch=(hl + 2) * row_b, src_ptr=e.data_ptr() + row_b)
+        return gat.full()
 
 
 # ------------------------------------------------------------------------------------------------ MoVQ

@@ -48,13 +48,21 @@ class Kandinsky2Config:
 class Kandinsky2Pipeline:
     def __init__(self, cfg: Kandinsky2Config = Kandinsky2Config(), backend: str = "native", device: str = "cuda",
                  dtype=torch.float16, seed: int = 0, model_dir: Optional[str] = None, use_graph: bool = True,
-                 cfg_parallel=None):
+                 cfg_parallel=None, patch_parallel=None):
         """``cfg_parallel``: a 2-rank ``PeerHeap`` — the two classifier-free-guidance branches of every decoder-UNet step
         run on two GPUs and exchange their predictions through peer memory (as in ``SD15Pipeline``); text encoder,
-        prior and MoVQ are small and run whole on both. Same bytes as one GPU."""
+        prior and MoVQ are small and run whole on both. Same bytes as one GPU.
+        ``patch_parallel``: a 2/4/8-rank ``PeerHeap`` — ONE image over those GPUs, the decoder UNet split into row bands
+        (parallel/patch.py: GroupNorm moments, conv halo rows and attention K/V cross ranks through peer memory with
+        in-kernel flag waits). Text encoder, prior and MoVQ run whole on every rank. Same bytes as one GPU."""
         self.cfg, self.backend, self.device, self.dtype = cfg, backend, torch.device(device), dtype
         self.cfgp = cfg_parallel
         assert cfg_parallel is None or (cfg_parallel.world == 2 and backend == "native"), "cfg_parallel needs a 2-rank heap"
+        self.pp = None
+        if patch_parallel is not None:
+            assert backend == "native" and cfg_parallel is None
+            from ...parallel.patch import PatchContext
+            self.pp = PatchContext(patch_parallel, dtype)
         self.tokenizer = HashTokenizer(cfg.text.vocab_size, 77)
         with torch.device(device):
             unet, prior = KandinskyUNet(cfg.unet), DiffusionPrior(cfg.prior, text_dim=cfg.text.hidden)
@@ -166,7 +174,10 @@ class Kandinsky2Pipeline:
             for b in range(2):
                 ops.lincomb(None, [(1.0, f["x"])], dst_m=st["xin"][b], m_scale=sch.input_scale(i))
             emb_all = self.unet.embeddings(st["tvec"][2 * i:2 * i + 2], cond)
-            if self.cfgp is None:
+            if self.pp is not None:
+                e = self.unet.forward_patch(self.pp, st["xin"], emb_all)
+                ops.cfg_step(e[1], e[0], None, g=c.guidance, eps_out=f["eps"])
+            elif self.cfgp is None:
                 e = self.unet.forward(st["xin"], emb_all)
                 ops.cfg_step(e[1], e[0], None, g=c.guidance, eps_out=f["eps"])
             else:
@@ -225,6 +236,8 @@ class Kandinsky2Pipeline:
                 st["ex"], st["ex_off"] = self.cfgp.alloc((2, 1, h, w, 4), dt)      # same offset on both ranks
             if self.cfgp is not None:
                 self.cfgp.dry_run(lambda: self._run_native(st))
+            if self.pp is not None:
+                self.pp.heap.dry_run(lambda: self._run_native(st))
             if self.use_graph:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())

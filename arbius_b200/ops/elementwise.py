@@ -104,10 +104,11 @@ def finalize_u8(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def upsample_nearest2x(x: torch.Tensor) -> torch.Tensor:
+def upsample_nearest2x(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     lib = native.load()
     n, h, w, c = x.shape
-    y = torch.empty((n, 2 * h, 2 * w, c), dtype=x.dtype, device=x.device)
+    y = out if out is not None else torch.empty((n, 2 * h, 2 * w, c), dtype=x.dtype, device=x.device)
+    assert x.is_contiguous() and y.is_contiguous() and y.shape == (n, 2 * h, 2 * w, c)
     native.check(lib.ab_upsample_nearest2x(x.data_ptr(), y.data_ptr(), n, h, w, c, native.dtype_code(x.dtype),
                                            native.stream_ptr()), "ab_upsample_nearest2x")
     return y

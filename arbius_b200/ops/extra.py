@@ -27,9 +27,10 @@ def _lib():
     return lib
 
 
-def avgpool2x(x: torch.Tensor) -> torch.Tensor:
+def avgpool2x(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     n, h, w, c = x.shape
-    y = torch.empty((n, h // 2, w // 2, c), dtype=x.dtype, device=x.device)
+    y = out if out is not None else torch.empty((n, h // 2, w // 2, c), dtype=x.dtype, device=x.device)
+    assert x.is_contiguous() and y.is_contiguous() and y.shape == (n, h // 2, w // 2, c)
     native.check(_lib().ab_avgpool2x(x.data_ptr(), y.data_ptr(), n, h, w, c, native.dtype_code(x.dtype),
                                      native.stream_ptr()), "ab_avgpool2x")
     return y

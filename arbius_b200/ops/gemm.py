@@ -187,8 +187,10 @@ def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
 def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
             x2: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
             rowbias: Optional[torch.Tensor] = None, act: Optional[str] = None, out_scale: float = 1.0,
-            splitk: int = 0, block_n: int = 0, halo: bool = False) -> torch.Tensor:
+            splitk: int = 0, block_n: int = 0, halo: bool = False, sync=None) -> torch.Tensor:
     """3x3 / pad 1 / stride 1 implicit-GEMM conv. x [B,H,W,C1] (+ x2 [B,H,W,C2]), w_packed [Cout, 9*(C1+C2)].
+    ``sync``: (tick_ptr, site_ptr, mask) — the kernel's TMA producer waits for those ranks' flags before its first load
+    (the neighbours push their edge rows straight into this buffer's halo rows; parallel/patch.py).
     ``halo``: x (and x2) are [B, H + 2, W, C] — a row band of the image with the neighbouring bands' edge rows (or zeros
     at the image's top and bottom) in rows 0 and H+1, as a patch-parallel rank holds it; ``batch_scale`` then counts
     the bands, so the split-K choice is the whole image's."""
@@ -207,6 +209,8 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     a.M, a.N, a.K1, a.K2 = b * h * wd, n, c1, c2
     a.conv, a.nimg, a.H, a.W = 1, b, h, wd
     a.halo = 1 if halo else 0
+    if sync is not None:
+        a.sync_tick, a.sync_wait, a.sync_wait_mask = sync
     a.act, a.geglu, a.out_scale = ACT[act], 0, out_scale
     a.dtype = native.dtype_code(x.dtype)
     a.block_n = block_n

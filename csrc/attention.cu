@@ -36,6 +36,13 @@ struct AttnParams {
     float scale_log2;   // softmax scale * log2(e)
     int causal;
     int tiles_per_src;  // multi-source K/V: 128-key tiles held by each source (patch-parallel ranks)
+    // segmented keys [prefix | pixels] (SegMaps): the prefix fills its own tiles, pixel tiles count from pixel 0 and may
+    // straddle sources; K / V of head h are heads pk0 + h / pv0 + h of the prefix buffer, k0 + h / v0 + h of a pixel buffer
+    int prefix_len, prefix_tiles, pix_len, rows_per_src, nsrc;
+    int pk0, pv0, k0, v0;
+    const unsigned int* tick;        // cross-GPU flags: wait for source s (s != self_rank) before the first load from it
+    const unsigned int* wait_site;
+    int self_rank;
 };
 
 template <int NCH, typename T>
@@ -366,7 +373,7 @@ extern "C" int ab_flash_attn_multi(const ab_attn_args* a, const void* const* k_p
             if (mk(&kv.k[s], k_ptrs[s], lk_per_src, a->k_bs, a->k_ls)) return -1;             \
             if (mk(&kv.v[s], v_ptrs[s], lk_per_src, a->v_bs, a->v_ls)) return -1;             \
         }                                                                                     \
-        return launch_attn2_multi<T, N>(tq, kv, p, stream);                                   \
+        return launch_attn2_multi<T, KvMaps<N>>(tq, kv, p, stream);                                   \
     }
 #define AB_ATT_MULTI_T(T)                                  \
     switch (nsrc) {                                        \
@@ -378,4 +385,53 @@ extern "C" int ab_flash_attn_multi(const ab_attn_args* a, const void* const* k_p
     if (a->dtype == AB_BF16) { AB_ATT_MULTI_T(__nv_bfloat16) } else { AB_ATT_MULTI_T(__half) }
 #undef AB_ATT_MULTI_T
 #undef AB_ATT_MULTI
+}
+
+// ---- segmented keys: [prefix | pixel bands on 1..8 GPUs] (see include/arbius_b200.h) ------------------------------
+extern "C" int ab_flash_attn_segs(const ab_attn_segs_args* a, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && a->q && a->out, "null pointer");
+    AB_REQUIRE(a->nsrc == 1 || a->nsrc == 2 || a->nsrc == 4 || a->nsrc == 8, "nsrc must be 1, 2, 4 or 8");
+    AB_REQUIRE(a->head_dim % 8 == 0 && a->head_dim >= 16 && a->head_dim <= 64, "segmented attention needs head_dim in [16,64]");
+    AB_REQUIRE(a->lq > 0 && a->batch > 0 && a->heads > 0, "bad shape");
+    AB_REQUIRE(a->rows_per_src > 0 && (a->nsrc == 1 || a->rows_per_src % 8 == 0), "rows per source must be a multiple of 8");
+    AB_REQUIRE(a->prefix_len >= 0 && (a->prefix_len == 0 || a->prefix), "prefix missing");
+    AB_REQUIRE(a->q_ls % 8 == 0 && a->o_ls % 8 == 0 && a->pix_ls % 8 == 0 && a->pix_bs % 8 == 0, "strides must be multiples of 8");
+    AB_REQUIRE(!a->wait_site || a->tick, "wait_site needs tick");
+    const int D = a->head_dim;
+    AttnParams p{};
+    p.out = a->out; p.batch = a->batch; p.heads = a->heads; p.lq = a->lq; p.head_dim = D;
+    p.o_bs = a->o_bs; p.o_ls = a->o_ls;
+    const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
+    p.scale_log2 = scale * 1.4426950408889634f;
+    p.causal = 0;
+    p.prefix_len = a->prefix_len; p.prefix_tiles = (a->prefix_len + ATT_BN - 1) / ATT_BN;
+    p.pix_len = a->nsrc * a->rows_per_src; p.rows_per_src = a->rows_per_src; p.nsrc = a->nsrc;
+    p.lk = p.prefix_len + p.pix_len;
+    p.pk0 = a->prefix_k_head0; p.pv0 = a->prefix_v_head0; p.k0 = a->k_head0; p.v0 = a->v_head0;
+    p.tick = a->tick; p.wait_site = a->wait_site; p.self_rank = a->self_rank;
+    auto mk = [&](CUtensorMap* tm, const void* base, int heads_total, int L, long long bs, long long ls, uint32_t rows) {
+        uint64_t dims[4] = {(uint64_t)D, (uint64_t)heads_total, (uint64_t)L, (uint64_t)a->batch};
+        uint64_t str[3] = {(uint64_t)D * 2, (uint64_t)ls * 2, (uint64_t)(a->batch > 1 ? bs : ls * L) * 2};
+        uint32_t box[4] = {64, 1, rows, 1};
+        return ab_make_tensor_map(tm, a->dtype, 4, base, dims, str, box, 128);
+    };
+    CUtensorMap tq;
+    if (mk(&tq, a->q, a->heads, a->lq, a->q_bs, a->q_ls, 128)) return -1;
+    SegMaps kv;
+    for (int s = 0; s < a->nsrc; ++s) {
+        AB_REQUIRE(a->pix[s], "missing pixel source");
+        if (mk(&kv.big[1 + s], a->pix[s], a->heads_total, a->rows_per_src, a->pix_bs, a->pix_ls, 128)) return -1;
+        if (mk(&kv.small[1 + s], a->pix[s], a->heads_total, a->rows_per_src, a->pix_bs, a->pix_ls, 8)) return -1;
+    }
+    for (int s = a->nsrc; s < 8; ++s) { kv.big[1 + s] = kv.big[1]; kv.small[1 + s] = kv.small[1]; }
+    if (a->prefix_len > 0) {
+        if (mk(&kv.big[0], a->prefix, a->prefix_heads_total, a->prefix_len, a->prefix_bs, a->prefix_ls, 128)) return -1;
+    } else {
+        kv.big[0] = kv.big[1];
+    }
+    kv.small[0] = kv.small[1];
+    if (a->dtype == AB_BF16) return launch_attn2_multi<__nv_bfloat16, SegMaps>(tq, kv, p, stream);
+    return launch_attn2_multi<__half, SegMaps>(tq, kv, p, stream);
 }

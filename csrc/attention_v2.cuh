@@ -49,16 +49,30 @@ __device__ __forceinline__ float max3f(float a, float b, float c) {
 // K/V may live in up to NSRC buffers (one per GPU of a patch-parallel subset, peer-mapped over NVLink):
 // KV tile j comes from source j / tiles_per_src. The tile ORDER is global and fixed, so the result is
 // bit-identical however the keys are spread over GPUs — the all-gather is the TMA loads themselves.
-template <int NSRC>
+template <int NSRC_>
 struct KvMaps {
-    CUtensorMap k[NSRC];
-    CUtensorMap v[NSRC];
+    static constexpr bool kSegs = false;
+    static constexpr int NSRC = NSRC_;
+    CUtensorMap k[NSRC_];
+    CUtensorMap v[NSRC_];
+};
+// Segmented keys [prefix | pixels]: map 0 = the prefix buffer (replicated on every GPU), maps 1..8 = the pixel bands'
+// fused projections ([B, rows, heads_total, D]; K and V are head ranges of the same buffer). `big` boxes hold 128 rows
+// (a whole KV tile from one source), `small` boxes 8 rows (one swizzle atom: a tile that straddles two GPUs is
+// assembled from sixteen of them). The tile sequence — prefix tiles, then pixel tiles of 128 from pixel 0 — is the
+// same for every split, so the bytes are too.
+struct SegMaps {
+    static constexpr bool kSegs = true;
+    static constexpr int NSRC = 8;
+    CUtensorMap big[9];
+    CUtensorMap small[9];
 };
 
-template <typename T, int NSRC>
+template <typename T, typename KV>
 __global__ void __launch_bounds__(A2_THREADS, 1)
-flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ KvMaps<NSRC> kv,
+flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ KV kv,
                    const AttnParams p) {
+    constexpr int NSRC = KV::NSRC;
     constexpr float kRescaleThreshold = 8.0f;
 
     extern __shared__ uint8_t smem_raw[];
@@ -86,11 +100,16 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const bool b_active = q0 + 128 < p.lq;
     int kv_len = p.lk;
     if (p.causal) kv_len = min(p.lk, q0 + 256);
-    const int NT = (kv_len + ATT_BN - 1) / ATT_BN;
+    int NT = (kv_len + ATT_BN - 1) / ATT_BN;
+    if constexpr (KV::kSegs) NT = p.prefix_tiles + (p.pix_len + ATT_BN - 1) / ATT_BN;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
-        for (int s = 0; s < NSRC; ++s) { tma_prefetch_desc(&kv.k[s]); tma_prefetch_desc(&kv.v[s]); }
+        if constexpr (KV::kSegs) {
+            for (int s = 0; s <= p.nsrc; ++s) { tma_prefetch_desc(&kv.big[s]); tma_prefetch_desc(&kv.small[s]); }
+        } else {
+            for (int s = 0; s < NSRC; ++s) { tma_prefetch_desc(&kv.k[s]); tma_prefetch_desc(&kv.v[s]); }
+        }
         mbar_init(q_full, 1);
         for (int s = 0; s < A2_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
         for (int t = 0; t < 2; ++t) { mbar_init(&s_full[t], 1); mbar_init(&p_full[t], 128); mbar_init(&o_full[t], 1); }
@@ -110,13 +129,55 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
             if (b_active) tma_load_4d(sQ + CHUNK_BYTES, &tmQ, q_full, 0, h, q0 + 128, b);
             int stage = 0; uint32_t phase = 0;
+            unsigned int waited = 0;
+            unsigned int tick = 0;
+            if constexpr (KV::kSegs) { if (p.wait_site) tick = *p.tick; }
             for (int j = 0; j < NT; ++j) {
                 mbar_wait(&kv_empty[stage], phase ^ 1);
                 mbar_expect_tx(&kv_full[stage], 2 * CHUNK_BYTES);
-                int src = 0, row = j * ATT_BN;
-                if (NSRC > 1) { src = j / p.tiles_per_src; row = (j - src * p.tiles_per_src) * ATT_BN; }
-                tma_load_4d(sK + stage * CHUNK_BYTES, &kv.k[src], &kv_full[stage], 0, h, row, b);
-                tma_load_4d(sV + stage * CHUNK_BYTES, &kv.v[src], &kv_full[stage], 0, h, row, b);
+                if constexpr (KV::kSegs) {
+                    uint8_t* dk = sK + stage * CHUNK_BYTES;
+                    uint8_t* dv = sV + stage * CHUNK_BYTES;
+                    // a peer's K/V rows may only be read once its flag has arrived (one wait per source and CTA)
+                    auto need = [&](int s) {
+                        if (p.wait_site && s != p.self_rank && !((waited >> s) & 1u)) {
+                            sync_wait_flags(p.wait_site, 1u << s, tick);
+                            fence_proxy_async_all();
+                            waited |= 1u << s;
+                        }
+                    };
+                    if (j < p.prefix_tiles) {
+                        tma_load_4d(dk, &kv.big[0], &kv_full[stage], 0, p.pk0 + h, j * ATT_BN, b);
+                        tma_load_4d(dv, &kv.big[0], &kv_full[stage], 0, p.pv0 + h, j * ATT_BN, b);
+                    } else {
+                        const int g0 = (j - p.prefix_tiles) * ATT_BN;
+                        const int g1 = min(g0 + ATT_BN, p.pix_len) - 1;           // last valid pixel row of the tile
+                        const int s0 = g0 / p.rows_per_src, s1 = g1 / p.rows_per_src;
+                        if (s0 == s1) {
+                            // whole tile from one GPU (rows past the end of the last band are zero-filled by TMA)
+                            need(s0);
+                            tma_load_4d(dk, &kv.big[1 + s0], &kv_full[stage], 0, p.k0 + h, g0 - s0 * p.rows_per_src, b);
+                            tma_load_4d(dv, &kv.big[1 + s0], &kv_full[stage], 0, p.v0 + h, g0 - s0 * p.rows_per_src, b);
+                        } else {
+                            // the tile straddles GPUs: sixteen 8-row boxes, each from the band that owns its rows
+#pragma unroll 1
+                            for (int bb = 0; bb < ATT_BN / 8; ++bb) {
+                                const int g = g0 + 8 * bb;
+                                int s = g / p.rows_per_src;
+                                int row = g - s * p.rows_per_src;
+                                if (g >= p.pix_len) { s = p.nsrc - 1; row = p.rows_per_src + 8; }   // out of bounds: zeros
+                                else need(s);
+                                tma_load_4d(dk + bb * 1024, &kv.small[1 + s], &kv_full[stage], 0, p.k0 + h, row, b);
+                                tma_load_4d(dv + bb * 1024, &kv.small[1 + s], &kv_full[stage], 0, p.v0 + h, row, b);
+                            }
+                        }
+                    }
+                } else {
+                    int src = 0, row = j * ATT_BN;
+                    if (NSRC > 1) { src = j / p.tiles_per_src; row = (j - src * p.tiles_per_src) * ATT_BN; }
+                    tma_load_4d(sK + stage * CHUNK_BYTES, &kv.k[src], &kv_full[stage], 0, h, row, b);
+                    tma_load_4d(sV + stage * CHUNK_BYTES, &kv.v[src], &kv_full[stage], 0, h, row, b);
+                }
                 if (++stage == A2_STAGES) { stage = 0; phase ^= 1; }
             }
         }
@@ -189,9 +250,15 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             for (int j = 0; j < NT; ++j) {
                 mbar_wait(&s_full[t], j & 1);
                 tc_fence_after();
-                const int col0 = j * ATT_BN;
+                int col0 = j * ATT_BN;
                 int col_hi = p.lk;
                 if (p.causal) col_hi = min(col_hi, qrow + 1);
+                if constexpr (KV::kSegs) {
+                    // every tile counts its own valid keys: a short prefix tile, full pixel tiles, a short last one
+                    col0 = 0;
+                    col_hi = j < p.prefix_tiles ? min(ATT_BN, p.prefix_len - j * ATT_BN)
+                                                : min(ATT_BN, p.pix_len - (j - p.prefix_tiles) * ATT_BN);
+                }
                 const bool full_tile = __all_sync(0xffffffffu, col0 + ATT_BN <= col_hi);
                 // ---- pass 1: raw row max ----
                 // Both passes are software-pipelined over the four 32-column chunks: the tcgen05.ld of chunk c+1 is in
@@ -327,12 +394,12 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
-template <typename T, int NSRC>
-static int launch_attn2_multi(const CUtensorMap& tq, const KvMaps<NSRC>& kv, const AttnParams& p, cudaStream_t stream) {
+template <typename T, typename KV>
+static int launch_attn2_multi(const CUtensorMap& tq, const KV& kv, const AttnParams& p, cudaStream_t stream) {
     constexpr int smem = (2 + 2 * A2_STAGES + 4) * CHUNK_BYTES + 16 * 8 + 16 + 1024;
-    if (ab_ensure_max_smem(reinterpret_cast<const void*>(flash_attn2_kernel<T, NSRC>), smem)) return -1;
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(flash_attn2_kernel<T, KV>), smem)) return -1;
     dim3 grid((p.lq + 255) / 256, p.heads, p.batch);
-    AB_CHECK_CUDA(launch_pdl(flash_attn2_kernel<T, NSRC>, grid, dim3(A2_THREADS), smem, stream, tq, kv, p));
+    AB_CHECK_CUDA(launch_pdl(flash_attn2_kernel<T, KV>, grid, dim3(A2_THREADS), smem, stream, tq, kv, p));
     ab_count_launch(1);
     return 0;
 }
@@ -343,5 +410,5 @@ static int launch_attn2(const CUtensorMap& tq, const CUtensorMap& tk, const CUte
     KvMaps<1> kv;
     kv.k[0] = tk;
     kv.v[0] = tv;
-    return launch_attn2_multi<T, 1>(tq, kv, p, stream);
+    return launch_attn2_multi<T, KvMaps<1>>(tq, kv, p, stream);
 }

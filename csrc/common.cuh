@@ -300,6 +300,40 @@ __device__ __forceinline__ float apply_act(float x, int act) {
     }
 }
 
+// ---- cross-GPU flags (patch parallelism: no barrier launches between operators) ------------------------------
+// A "site" is a block of 16 u32 at the same heap offset on every GPU: word r is written only by rank r (over NVLink,
+// into the copy of the GPU that will wait on it) and carries the value of a pass counter ("tick") that every GPU
+// advances in step; word 8 is a local arrival counter for "last CTA signals". A producer publishes with a
+// system-scope release after its data stores; a consumer spins with system-scope acquires on its OWN copy.
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// orders global-memory accesses of the generic proxy (flag acquire, peers' plain stores) before later TMA accesses
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// Spin until every rank in `mask` has published a value >= tick in this GPU's copy of the site. Bounded: a protocol
+// bug or a dead peer traps (~60 s) instead of hanging the box.
+__device__ __forceinline__ void sync_wait_flags(const unsigned int* site, unsigned int mask, unsigned int tick) {
+    while (mask) {
+        const int r = __ffs(mask) - 1;
+        mask &= mask - 1;
+        if (static_cast<int>(ld_acquire_sys_u32(site + r) - tick) >= 0) continue;
+        const long long t0 = clock64();
+        while (static_cast<int>(ld_acquire_sys_u32(site + r) - tick) < 0) {
+            __nanosleep(20);
+            if (clock64() - t0 > 120000000000LL) {
+                printf("sync_wait_flags timeout: waiting for rank %d tick %u (have %u) block %d\n", r, tick,
+                       ld_acquire_sys_u32(site + r), blockIdx.x);
+                __trap();
+            }
+        }
+    }
+}
+
 // ---- programmatic dependent launch ------------------------------------------------------------
 // A kernel launched through launch_pdl() may become resident while its predecessor in the stream is still
 // draining; everything before pdl_wait() (barrier init, TMEM alloc, descriptor prefetch) overlaps that tail.

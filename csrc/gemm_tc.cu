@@ -61,6 +61,11 @@ struct GemmParams {
     // scattered over 32 rows per warp instruction. Off for GEGLU, split-K partials and reduce-scatter.
     int tma_store;
     int mt;                     // 128-row M tiles per CTA (1 or 2)
+    // cross-GPU hand-off folded into the kernel (patch parallelism): the producer thread waits for the ranks in
+    // sync_wait_mask to publish *sync_tick in this GPU's copy of the site before its first load (halo rows arrived)
+    const unsigned int* sync_tick;
+    const unsigned int* sync_wait;
+    unsigned int sync_wait_mask;
     alignas(64) CUtensorMap amaps[8];
     alignas(64) CUtensorMap omap;
 };
@@ -243,6 +248,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0) {
         // ================= TMA producer =================
         if (lane == 0) {
+            if (p.sync_wait) {
+                sync_wait_flags(p.sync_wait, p.sync_wait_mask, *p.sync_tick);
+                fence_proxy_async_all();      // the peers' plain stores (acquired above) before this thread's TMA reads
+            }
             int stage = 0;
             uint32_t phase = 0;
             for (int kc = kc_begin; kc < kc_end; ++kc) {
@@ -634,6 +643,8 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     p.out = a->out; p.bias = a->bias; p.rowbias = a->rowbias; p.residual = a->residual;
     p.workspace = reinterpret_cast<float*>(a->workspace);
     p.dbg = g_gemm_dbg;
+    p.sync_tick = a->sync_tick; p.sync_wait = a->sync_wait; p.sync_wait_mask = a->sync_wait_mask;
+    AB_REQUIRE(!a->sync_wait || a->sync_tick, "sync_wait needs sync_tick");
     p.M = a->M; p.N = a->N; p.Nout = a->geglu ? a->N / 2 : a->N;
     p.taps = a->conv == 2 ? 3 : (a->conv ? 9 : 1);
     p.k1_chunks = (a->K2 > 0 || a->conv) ? a->K1 / BK : (a->K1 + BK - 1) / BK;

@@ -536,6 +536,254 @@ __global__ void __launch_bounds__(GN_THREADS) gn_fused_kernel(const GnParams p, 
     }
 }
 
+// ---- patch-parallel GroupNorm: statistics, the exchange between the GPUs, and apply in ONE launch ----------------
+// One image's rows are spread over `world` GPUs in row bands; this GPU holds canonical shards
+// [shard_base, shard_base + ns_local). Phase 1 is gn_fused_kernel's (same items, same arithmetic), and every item's
+// moments are also stored into each peer's partial array. After a local grid barrier CTA 0 publishes the tick to every
+// peer; every CTA then waits until all peers' ticks have arrived in this GPU's copy of the site — the peers' moments
+// were stored before their ticks — merges the 8 shards in canonical order and normalises its rows. Rows at the band's
+// edges are additionally stored into the neighbours' halo slots, and the last CTA to finish publishes "rows written":
+// the consumer (the next conv's TMA producer warp, or a gather) waits on that. No barrier kernel on either side.
+struct GnPatch {
+    float4* part_peers[8];
+    const unsigned int* tick;
+    unsigned int* stats_sites[8];
+    void* up_halo; void* down_halo;
+    int halo_rows;
+    unsigned int* done_sites[8];
+    unsigned int* done_local;
+    int world, rank, dry;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, const __grid_constant__ GnPatch x,
+                                                              unsigned int* bar, int cache_rows) {
+    extern __shared__ __align__(16) unsigned char gn_smem[];
+    __shared__ GnMoments shard_mom[GN_SHARDS][GN_MAX_GROUPS + 1];
+    __shared__ float2 s_stats[GN_MAX_GROUPS];
+    const int C = p.c1 + p.c2;
+    const int ncol = C / 8;
+    const int cpg = C / p.groups;
+    const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
+    const int passes = (ncol + GN_THREADS - 1) / GN_THREADS;
+    float* s_sum = reinterpret_cast<float*>(gn_smem);
+    float* s_sq = s_sum + RL * C;
+    uint4* cache = reinterpret_cast<uint4*>(gn_smem + static_cast<size_t>(2) * RL * C * sizeof(float));   // [rows][ncol]
+    const int ns = p.ns_local;
+    const int items_per_img = ns * p.sub;
+    const int total_items = p.n * items_per_img;
+    const bool use_cache = cache_rows > 0;
+    const unsigned int tick = x.tick ? *x.tick : 0u;
+
+    auto item_rows = [&](int item, int& n, int& shard, int& sb, int& r0, int& r1) {
+        n = item / items_per_img;
+        const int rem = item - n * items_per_img;
+        shard = rem / p.sub; sb = rem - shard * p.sub;
+        const int s_begin = static_cast<int>((static_cast<long long>(shard) * p.hw) / ns);
+        const int s_end = static_cast<int>((static_cast<long long>(shard + 1) * p.hw) / ns);
+        const int len = s_end - s_begin;
+        r0 = s_begin + static_cast<int>((static_cast<long long>(sb) * len) / p.sub);
+        r1 = s_begin + static_cast<int>((static_cast<long long>(sb + 1) * len) / p.sub);
+    };
+
+    // ---------------- phase 1: per-item moments (+ keep the rows), pushed to every GPU ----------------
+    int cached = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        int n, shard, sb, r0, r1;
+        item_rows(item, n, shard, sb, r0, r1);
+        const T* x1 = reinterpret_cast<const T*>(p.x) + static_cast<long long>(n) * p.hw * p.c1;
+        const T* x2 = p.x2 ? reinterpret_cast<const T*>(p.x2) + static_cast<long long>(n) * p.hw * p.c2 : nullptr;
+        for (int pass = 0; pass < passes; ++pass) {
+            int vc, rl;
+            bool active;
+            if (passes == 1) { vc = threadIdx.x % ncol; rl = threadIdx.x / ncol; active = rl < RL; }
+            else { vc = pass * GN_THREADS + threadIdx.x; rl = 0; active = vc < ncol; }
+            if (active) {
+                const int c = vc * 8;
+                const T* src; int ld, cc;
+                if (c < p.c1) { src = x1; ld = p.c1; cc = c; } else { src = x2; ld = p.c2; cc = c - p.c1; }
+                float s[8], q[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
+                const T* ptr = src + static_cast<long long>(r0 + rl) * ld + cc;
+                const long long step = static_cast<long long>(RL) * ld;
+                uint4* cp = cache + static_cast<long long>(cached + rl) * ncol + vc;
+                const long long cstep = static_cast<long long>(RL) * ncol;
+                int r = r0 + rl;
+                for (; r + 3 * RL < r1; r += 4 * RL) {
+                    uint4 v0 = *reinterpret_cast<const uint4*>(ptr);
+                    uint4 v1 = *reinterpret_cast<const uint4*>(ptr + step);
+                    uint4 v2 = *reinterpret_cast<const uint4*>(ptr + 2 * step);
+                    uint4 v3 = *reinterpret_cast<const uint4*>(ptr + 3 * step);
+                    ptr += 4 * step;
+                    if (use_cache) { cp[0] = v0; cp[cstep] = v1; cp[2 * cstep] = v2; cp[3 * cstep] = v3; cp += 4 * cstep; }
+                    float f[8];
+                    unpack8<T>(v0, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                    unpack8<T>(v1, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                    unpack8<T>(v2, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                    unpack8<T>(v3, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                }
+                for (; r < r1; r += RL) {
+                    const uint4 v = *reinterpret_cast<const uint4*>(ptr);
+                    ptr += step;
+                    if (use_cache) { cp[0] = v; cp += cstep; }
+                    float f[8];
+                    unpack8<T>(v, f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s_sum[rl * C + c + i] = s[i]; s_sq[rl * C + c + i] = q[i]; }
+            }
+        }
+        __syncthreads();
+        const long long pidx = ((static_cast<long long>(n) * GN_SHARDS + p.shard_base + shard) * p.sub + sb) * p.groups;
+        gn_block_moments(s_sum, s_sq, RL, C, cpg, p.groups, r1 - r0, p.partials + pidx);
+        __syncthreads();
+        for (int t = threadIdx.x; t < p.groups * x.world; t += GN_THREADS) {
+            const int peer = t / p.groups, g = t - peer * p.groups;
+            if (peer != x.rank) x.part_peers[peer][pidx + g] = p.partials[pidx + g];
+        }
+        __threadfence_system();
+        __syncthreads();
+        cached += r1 - r0;
+    }
+
+    const T* gamma = reinterpret_cast<const T*>(p.gamma);
+    const T* beta = reinterpret_cast<const T*>(p.beta);
+    uint4 h_gamma = make_uint4(0, 0, 0, 0), h_beta = make_uint4(0, 0, 0, 0);
+    if (passes == 1 && threadIdx.x / ncol < RL) {
+        const int c_h = (threadIdx.x % ncol) * 8;
+        if (gamma) h_gamma = __ldg(reinterpret_cast<const uint4*>(gamma + c_h));
+        if (beta) h_beta = __ldg(reinterpret_cast<const uint4*>(beta + c_h));
+    }
+
+    gn_grid_barrier(bar, gridDim.x);          // every local item's moments are stored here and on every peer
+    if (!x.dry) {
+        if (blockIdx.x == 0 && threadIdx.x < x.world && threadIdx.x != x.rank) {
+            __threadfence_system();
+            st_release_sys_u32(x.stats_sites[threadIdx.x] + x.rank, tick);
+        }
+        if (threadIdx.x < x.world && threadIdx.x != x.rank) sync_wait_flags(x.stats_sites[x.rank], 1u << threadIdx.x, tick);
+        __syncthreads();
+    }
+
+    // ---------------- phase 2 + 3: merge all 8 shards in canonical order, normalise, push the edge rows ----------------
+    const T* scale = reinterpret_cast<const T*>(p.scale);
+    const T* shift = reinterpret_cast<const T*>(p.shift);
+    const long long y_bs = p.y_bs > 0 ? p.y_bs : static_cast<long long>(p.hw) * C;
+    const int lo_edge = x.halo_rows, hi_edge = p.hw - x.halo_rows;
+    int stats_n = -1;
+    cached = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        int n, shard, sb, r0, r1;
+        item_rows(item, n, shard, sb, r0, r1);
+        if (n != stats_n) {
+            __syncthreads();
+            const float4* part = p.partials + static_cast<long long>(n) * GN_SHARDS * p.sub * p.groups;
+            for (int idx = threadIdx.x; idx < GN_SHARDS * p.groups; idx += GN_THREADS) {
+                const int sh = idx / p.groups, g = idx % p.groups;
+                GnMoments acc{0.f, 0.f, 0.f};
+                for (int sb0 = 0; sb0 < p.sub; sb0 += 8) {
+                    float4 q4[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (sb0 + u < p.sub) q4[u] = __ldcg(&part[(sh * p.sub + sb0 + u) * p.groups + g]);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (sb0 + u < p.sub) acc = gn_merge(acc, GnMoments{q4[u].x, q4[u].y, q4[u].z});
+                }
+                shard_mom[sh][g] = acc;
+            }
+            __syncthreads();
+            if (threadIdx.x < p.groups) {
+                const int g = threadIdx.x;
+                GnMoments acc = shard_mom[0][g];
+#pragma unroll
+                for (int sh = 1; sh < GN_SHARDS; ++sh) acc = gn_merge(acc, shard_mom[sh][g]);
+                const float var = acc.m2 / acc.cnt;
+                s_stats[g] = make_float2(acc.mean, rsqrtf(var + p.eps));
+            }
+            __syncthreads();
+            stats_n = n;
+        }
+        T* y = reinterpret_cast<T*>(p.y) + static_cast<long long>(n) * y_bs;
+        T* y_up = x.up_halo ? reinterpret_cast<T*>(x.up_halo) + static_cast<long long>(n) * y_bs : nullptr;
+        T* y_dn = x.down_halo ? reinterpret_cast<T*>(x.down_halo) + static_cast<long long>(n) * y_bs : nullptr;
+        for (int pass = 0; pass < passes; ++pass) {
+            int vc, rl;
+            bool active;
+            if (passes == 1) { vc = threadIdx.x % ncol; rl = threadIdx.x / ncol; active = rl < RL; }
+            else { vc = pass * GN_THREADS + threadIdx.x; rl = 0; active = vc < ncol; }
+            if (!active) continue;
+            const int c = vc * 8;
+            const T* src; int ld, cc;
+            if (c < p.c1) { src = reinterpret_cast<const T*>(p.x) + static_cast<long long>(n) * p.hw * p.c1; ld = p.c1; cc = c; }
+            else { src = reinterpret_cast<const T*>(p.x2) + static_cast<long long>(n) * p.hw * p.c2; ld = p.c2; cc = c - p.c1; }
+            float a[8], b[8];
+            {
+                float ga[8], be[8], sc[8], sh[8];
+                if (gamma) unpack8<T>(passes == 1 ? h_gamma : __ldg(reinterpret_cast<const uint4*>(gamma + c)), ga);
+                if (beta) unpack8<T>(passes == 1 ? h_beta : __ldg(reinterpret_cast<const uint4*>(beta + c)), be);
+                if (scale) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(scale + static_cast<long long>(n) * p.ss + c)), sc);
+                if (shift) unpack8<T>(__ldg(reinterpret_cast<const uint4*>(shift + static_cast<long long>(n) * p.ss + c)), sh);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float2 st = s_stats[(c + i) / cpg];
+                    float ai = st.y, bi = -st.x * st.y;
+                    if (gamma) { ai *= ga[i]; bi *= ga[i]; }
+                    if (beta) bi += be[i];
+                    if (scale) { ai *= (1.0f + sc[i]); bi *= (1.0f + sc[i]); }
+                    if (shift) bi += sh[i];
+                    a[i] = ai; b[i] = bi;
+                }
+            }
+            for (int r = r0 + rl; r < r1; r += RL) {
+                float f[8], o[8];
+                const uint4 v = use_cache ? cache[static_cast<long long>(cached + (r - r0)) * ncol + vc]
+                                          : *reinterpret_cast<const uint4*>(src + static_cast<long long>(r) * ld + cc);
+                unpack8<T>(v, f);
+                if (p.act == ACT_SILU) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = act_silu(fmaf(f[i], a[i], b[i]));
+                } else if (p.act == ACT_NONE) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = fmaf(f[i], a[i], b[i]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) o[i] = apply_act(fmaf(f[i], a[i], b[i]), p.act);
+                }
+                const uint4 packed = pack8<T>(o);
+                *reinterpret_cast<uint4*>(y + static_cast<long long>(r) * C + c) = packed;
+                if (y_up && r < lo_edge) *reinterpret_cast<uint4*>(y_up + static_cast<long long>(r) * C + c) = packed;
+                if (y_dn && r >= hi_edge) *reinterpret_cast<uint4*>(y_dn + static_cast<long long>(r - hi_edge) * C + c) = packed;
+            }
+        }
+        cached += r1 - r0;
+    }
+    if (x.done_local && !x.dry) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            const unsigned int ticket = atomicAdd(x.done_local + 8, 1u);
+            if (ticket == gridDim.x - 1) {
+                x.done_local[8] = 0;
+                __threadfence_system();
+                for (int d = 0; d < x.world; ++d)
+                    if (x.done_sites[d]) st_release_sys_u32(x.done_sites[d] + x.rank, tick);
+            }
+        }
+    }
+}
+
 // ---- LayerNorm: one warp per row, row held in registers -----------------------------------------
 template <typename T, int MAXV>
 __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x, const T* __restrict__ gamma,
@@ -739,6 +987,72 @@ extern "C" int ab_groupnorm_sharded_apply(const ab_groupnorm_args* a, int world,
     if (a->dtype == AB_BF16) AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__nv_bfloat16>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     else AB_CHECK_CUDA(launch_pdl(gn_apply_kernel<__half>, blocks, dim3(GN_APPLY_THREADS), 0, stream, p));
     ab_count_launch(2);
+    return 0;
+}
+
+extern "C" int ab_groupnorm_patch(const ab_groupnorm_args* a, const ab_gn_patch_args* pa, void* stream_) {
+    using namespace ab;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    AB_REQUIRE(a && pa && a->x && a->y && a->partials, "null pointer");
+    AB_REQUIRE(pa->world == 2 || pa->world == 4 || pa->world == 8, "world must be 2, 4 or 8");
+    AB_REQUIRE(pa->rank >= 0 && pa->rank < pa->world, "bad rank");
+    const int C = a->c1 + a->c2;
+    AB_REQUIRE(a->n > 0 && a->hw > 0 && a->c1 > 0 && a->c1 % 8 == 0 && a->c2 % 8 == 0, "bad shape");
+    AB_REQUIRE(a->groups > 0 && a->groups <= GN_MAX_GROUPS && C % a->groups == 0, "bad group count");
+    AB_REQUIRE(a->c2 == 0 || a->x2, "x2 missing");
+    const int ns = GN_SHARDS / pa->world;
+    AB_REQUIRE(a->hw % ns == 0, "local rows must split evenly into this GPU's canonical shards");
+    AB_REQUIRE(pa->dry || pa->tick, "tick is required");
+    AB_REQUIRE(pa->halo_rows >= 0 && pa->halo_rows <= a->hw, "bad halo row count");
+    GnParams p{};
+    p.x = a->x; p.x2 = a->x2; p.y = a->y; p.gamma = a->gamma; p.beta = a->beta; p.scale = a->scale; p.shift = a->shift;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(a->partials);
+    p.counters = reinterpret_cast<unsigned int*>(ws);
+    p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
+    p.sub = gn_sub_blocks(a->hw * pa->world);
+    p.ns_local = ns; p.shard_base = pa->rank * ns;
+    p.eps = a->eps; p.act = a->act; p.ss = a->ss_stride > 0 ? a->ss_stride : C;
+    p.y_bs = pa->y_batch_stride;
+    GnPatch x{};
+    for (int r = 0; r < pa->world; ++r) {
+        AB_REQUIRE(pa->part_peers[r], "missing partial-moment array");
+        x.part_peers[r] = reinterpret_cast<float4*>(pa->part_peers[r]);
+        AB_REQUIRE(pa->dry || pa->stats_sites[r], "missing stats site");
+        x.stats_sites[r] = pa->stats_sites[r];
+        x.done_sites[r] = pa->done_sites[r];
+    }
+    p.partials = x.part_peers[pa->rank];
+    x.tick = pa->tick; x.up_halo = pa->up_halo; x.down_halo = pa->down_halo; x.halo_rows = pa->halo_rows;
+    x.done_local = pa->done_local; x.world = pa->world; x.rank = pa->rank; x.dry = pa->dry;
+    const int ncol = C / 8;
+    const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
+    const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
+    AB_REQUIRE(smem <= 48 * 1024, "channel count too large for the stats kernel");
+    const int n_sm = ab_sm_count();
+    const int total_items = a->n * ns * p.sub;
+    const int grid_f = total_items < n_sm ? total_items : n_sm;
+    const int items_per_cta = (total_items + grid_f - 1) / grid_f;
+    const int max_item_rows = (a->hw / ns + p.sub - 1) / p.sub + 1;
+    const long long need_rows = static_cast<long long>(items_per_cta) * max_item_rows;
+    const long long cap_rows = (200LL * 1024 - static_cast<long long>(smem)) / (static_cast<long long>(C) * 2);
+    const int cache_rows = need_rows <= cap_rows ? static_cast<int>(need_rows) : 0;   // 0: phase 3 re-reads the rows
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_patch_kernel<__half>), 200 * 1024)) return -1;
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_patch_kernel<__nv_bfloat16>), 200 * 1024)) return -1;
+    const size_t smem_f = smem + static_cast<size_t>(cache_rows) * C * 2;
+    unsigned int* bar = p.counters + a->n;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid_f);
+    cfg.blockDim = dim3(GN_THREADS);
+    cfg.dynamicSmemBytes = smem_f;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (a->dtype == AB_BF16) AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__nv_bfloat16>, p, x, bar, cache_rows));
+    else AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__half>, p, x, bar, cache_rows));
+    ab_count_launch(1);
     return 0;
 }
 

@@ -1,0 +1,130 @@
+// Cross-GPU hand-offs for patch parallelism (one image's row bands on 2/4/8 GPUs of an NVSwitch box) without
+// barrier launches: tick counter, flag publish / wait, and strided copies through peer memory with the flag wait in
+// their prologue and the flag publish in their epilogue. The GroupNorm, conv and attention kernels carry the same
+// wait / publish inside themselves (norm.cu, gemm_tc.cu, attention_v2.cuh); these small kernels cover the places where
+// the neighbour of a hand-off is an elementwise op. SURVEY §2.8 "patch parallelism", §5.9 item 3.
+// No counterpart in the reference (single GPU).
+#include <stdio.h>
+
+#include "../include/arbius_b200.h"
+#include "common.cuh"
+
+extern "C" void ab_count_launch(int n);
+
+namespace ab {
+
+__global__ void sync_tick_kernel(unsigned int* tick) { *tick = *tick + 1; }
+
+struct PeerSites { unsigned int* site[8]; };
+
+__global__ void sync_signal_kernel(const unsigned int* tick, PeerSites s, int world, int rank) {
+    const int t = threadIdx.x;
+    if (t < world && s.site[t]) {
+        __threadfence_system();
+        st_release_sys_u32(s.site[t] + rank, *tick);
+    }
+}
+
+__global__ void sync_wait_kernel(const unsigned int* tick, const unsigned int* site, unsigned int mask) {
+    const int t = threadIdx.x;
+    if (t < 8 && ((mask >> t) & 1u)) sync_wait_flags(site, 1u << t, *tick);
+}
+
+struct PatchCopyParams {
+    ab_copy_seg seg[16];
+    int nseg;
+    const unsigned int* tick;
+    const unsigned int* wait_site;
+    unsigned int wait_mask;
+    unsigned int* signal_sites[8];
+    int world, rank;
+    unsigned int* local_site;
+};
+
+__global__ void __launch_bounds__(256) patch_copy_kernel(const __grid_constant__ PatchCopyParams p) {
+    if (p.wait_site && p.wait_mask) {
+        if (threadIdx.x == 0) sync_wait_flags(p.wait_site, p.wait_mask, *p.tick);
+        __syncthreads();
+    }
+    for (int s = 0; s < p.nseg; ++s) {
+        const ab_copy_seg& g = p.seg[s];
+        const long long w16 = g.width_bytes >> 4, dp = g.dst_pitch >> 4, sp = g.src_pitch >> 4;
+        const long long total = w16 * g.rows;
+        uint4* dst = reinterpret_cast<uint4*>(g.dst);
+        const uint4* src = reinterpret_cast<const uint4*>(g.src);
+        for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
+            const long long r = i / w16, c = i - r * w16;
+            dst[r * dp + c] = src[r * sp + c];
+        }
+    }
+    if (p.local_site) {
+        // last CTA publishes: every CTA's stores are fenced to system scope before its arrival is counted
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            const unsigned int ticket = atomicAdd(p.local_site + 8, 1u);
+            if (ticket == gridDim.x - 1) {
+                p.local_site[8] = 0;
+                __threadfence_system();
+                const unsigned int t = *p.tick;
+                for (int d = 0; d < p.world; ++d)
+                    if (p.signal_sites[d]) st_release_sys_u32(p.signal_sites[d] + p.rank, t);
+            }
+        }
+    }
+}
+
+}  // namespace ab
+
+extern "C" int ab_sync_tick(unsigned int* tick, void* stream_) {
+    AB_REQUIRE(tick, "null tick");
+    ab::sync_tick_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(tick);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
+
+extern "C" int ab_sync_signal(const unsigned int* tick, unsigned int* const* peer_sites, int world, int rank, void* stream_) {
+    AB_REQUIRE(tick && peer_sites && world >= 1 && world <= 8 && rank >= 0 && rank < world, "bad arguments");
+    ab::PeerSites s{};
+    for (int d = 0; d < world; ++d) s.site[d] = peer_sites[d];
+    ab::sync_signal_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(tick, s, world, rank);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
+
+extern "C" int ab_sync_wait(const unsigned int* tick, const unsigned int* site, unsigned int mask, void* stream_) {
+    AB_REQUIRE(tick && site && mask < 256, "bad arguments");
+    ab::sync_wait_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(tick, site, mask);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}
+
+extern "C" int ab_patch_copy(const ab_patch_copy_args* a, void* stream_) {
+    using namespace ab;
+    AB_REQUIRE(a && a->nseg >= 0 && a->nseg <= 16, "bad segment count");
+    AB_REQUIRE((!a->wait_site && !a->local_site) || a->tick, "tick is required with wait or signal");
+    AB_REQUIRE(a->world >= 1 && a->world <= 8 && a->rank >= 0 && a->rank < a->world, "bad world / rank");
+    PatchCopyParams p{};
+    long long total = 0;
+    for (int s = 0; s < a->nseg; ++s) {
+        const ab_copy_seg& g = a->seg[s];
+        AB_REQUIRE(g.dst && g.src && g.rows > 0 && g.width_bytes > 0, "bad segment");
+        AB_REQUIRE(g.width_bytes % 16 == 0 && g.dst_pitch % 16 == 0 && g.src_pitch % 16 == 0 &&
+                   (reinterpret_cast<uintptr_t>(g.dst) & 15) == 0 && (reinterpret_cast<uintptr_t>(g.src) & 15) == 0,
+                   "16-byte alignment required");
+        p.seg[s] = g;
+        total += g.width_bytes / 16 * g.rows;
+    }
+    p.nseg = a->nseg; p.tick = a->tick; p.wait_site = a->wait_site; p.wait_mask = a->wait_mask;
+    for (int d = 0; d < 8; ++d) p.signal_sites[d] = d < a->world ? a->signal_sites[d] : nullptr;
+    p.world = a->world; p.rank = a->rank; p.local_site = a->local_site;
+    long long blocks = total / (256 * 4) + 1;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    patch_copy_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(p);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

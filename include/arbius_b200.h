@@ -69,6 +69,10 @@ typedef struct {
                              * zero padding: a row band of an image (patch parallelism) or the local frames of a clip
                              * (frame parallelism) with the neighbours' edge rows copied in from the GPUs next door.
                              * 0 or 1. */
+  /* optional cross-GPU wait folded into the kernel (see "cross-GPU flags" below): before its first load the TMA
+   * producer thread spins until every rank in sync_wait_mask has published *sync_tick in this GPU's copy of the
+   * site — the neighbours' halo rows, pushed straight into A's halo slots, have then arrived. NULL = no wait. */
+  const unsigned int* sync_tick; const unsigned int* sync_wait; unsigned int sync_wait_mask;
 } ab_gemm_args;
 int ab_gemm(const ab_gemm_args* args, void* stream);
 /* Multi-GPU forms of the same kernel (one NVSwitch box; pointers may be peer-mapped addresses).
@@ -122,6 +126,51 @@ size_t ab_groupnorm_partials_bytes(int n, int groups);
 int ab_groupnorm_sharded_stats(const ab_groupnorm_args* args, int world, int rank, void* partials_out, void* stream);
 int ab_groupnorm_sharded_apply(const ab_groupnorm_args* args, int world, void* const* part_srcs, long long y_batch_stride,
                                void* stream);
+/* ---- cross-GPU flags: patch parallelism without barrier launches (csrc/patch.cu) --------------------------------
+ * A row-band split of one image over 2/4/8 GPUs needs ~200 producer->consumer hand-offs per UNet step. Instead of a
+ * barrier kernel on each side of every one, producers publish a flag behind their data and consumers wait inside the
+ * kernel that needs the data. A "site" is 16 u32 at the same heap offset on every GPU (word r: written only by rank r,
+ * word 8: local arrival counter); flags carry a "tick" that every GPU advances once per UNet step (ab_sync_tick), so a
+ * captured CUDA graph replays correctly. No counterpart in the reference (single GPU). */
+int ab_sync_tick(unsigned int* tick, void* stream);
+/* publish *tick into word `rank` of each non-NULL site in peer_sites (entry d = rank d's copy of the site) */
+int ab_sync_signal(const unsigned int* tick, unsigned int* const* peer_sites, int world, int rank, void* stream);
+/* spin until every rank in mask has published *tick in this GPU's copy of the site */
+int ab_sync_wait(const unsigned int* tick, const unsigned int* site, unsigned int mask, void* stream);
+/* Strided copies whose source or destination may be peer memory, with the hand-off folded in: every CTA first waits
+ * (wait_site/wait_mask, optional), the segments are copied (rows x width_bytes each, 16-byte units), and the last CTA
+ * to finish publishes *tick to the sites in signal_sites (optional). `local_site` is this GPU's copy of the signalled
+ * site (its word 8 counts arrivals). Used for halo rows, for all-gathering the UNet's output bands and for gathering a
+ * level that is too small to split. */
+typedef struct { void* dst; const void* src; long long dst_pitch, src_pitch, width_bytes; int rows; } ab_copy_seg;
+typedef struct {
+  ab_copy_seg seg[16]; int nseg;
+  const unsigned int* tick;
+  const unsigned int* wait_site; unsigned int wait_mask;
+  unsigned int* signal_sites[8]; int world, rank;
+  unsigned int* local_site;
+} ab_patch_copy_args;
+int ab_patch_copy(const ab_patch_copy_args* args, void* stream);
+/* GroupNorm of a row band in ONE launch (patch parallelism): partial moments of this GPU's canonical shards are
+ * pushed into every peer's array, the peers' arrive the same way, all are merged in canonical order, the local rows
+ * are normalised. y may be the interior of a [n, H+2, W, C] halo buffer (y_batch_stride); with halo_rows > 0 the
+ * band's first / last halo_rows rows are also stored into the neighbours' halo slots (up_halo / down_halo: address of
+ * sample 0's slot on that GPU, batch stride y_batch_stride) and the last CTA publishes the tick to done_sites (the
+ * consumers' wait: the next conv's producer warp). args->hw is the LOCAL row count; args->partials the usual local
+ * workspace. Output bytes equal ab_groupnorm on the undivided tensor. dry != 0: no waits, no signals (module warm-up). */
+typedef struct {
+  int world, rank;
+  void* part_peers[8];            /* every rank's [n][8][sub][groups] float4 array (peer-mapped; [rank] = local) */
+  const unsigned int* tick;
+  unsigned int* stats_sites[8];   /* the stats site on every rank (peer-mapped; [rank] = local) */
+  long long y_batch_stride;       /* elements; 0 = hw * C */
+  void* up_halo; void* down_halo; int halo_rows;
+  unsigned int* done_sites[8];    /* who gets the "rows written" tick: neighbours (halo) or everyone (gather); NULL = skip */
+  unsigned int* done_local;       /* this GPU's copy of the done site */
+  int dry;
+} ab_gn_patch_args;
+int ab_groupnorm_patch(const ab_groupnorm_args* args, const ab_gn_patch_args* patch, void* stream);
+
 /* Same operation as ab_groupnorm for callers that cannot allocate device memory (a host whose arena
  * already owns all of HBM, a plain C caller with no allocator, a loop that cannot take the device-wide
  * sync of cudaMalloc). args->partials is ignored: the statistics scratch is a ~0.5 MB array compiled
@@ -177,6 +226,23 @@ int ab_flash_attn(const ab_attn_args* args, void* stream);
  * No counterpart in the reference. */
 int ab_flash_attn_multi(const ab_attn_args* args, const void* const* k_ptrs, const void* const* v_ptrs, int nsrc,
                         int lk_per_src, void* stream);
+/* Segmented keys: [prefix | pixels]. The prefix (text / image-embedding tokens, replicated on every GPU) fills its
+ * own KV tiles; the pixel keys follow in tiles of 128 counted from pixel 0 and live in nsrc buffers of rows_per_src
+ * rows each (row bands of a patch-parallel subset; rows_per_src % 8 == 0; a tile that straddles two GPUs is fetched
+ * in 8-row boxes). Every buffer is a fused projection [B, rows, heads_total, D]: K of head h is head k_head0 + h, V
+ * is v_head0 + h. wait_site/tick (optional): the producer warp waits for source s's flag before its first load from
+ * it (s != self_rank). The tile sequence does not depend on nsrc, so the bytes do not either. head_dim <= 64.
+ * No counterpart in the reference. */
+typedef struct {
+  const void* q; void* out;
+  int batch, heads, lq, head_dim;
+  long long q_bs, q_ls, o_bs, o_ls;
+  float scale; int dtype;
+  const void* prefix; int prefix_len; long long prefix_bs, prefix_ls; int prefix_heads_total, prefix_k_head0, prefix_v_head0;
+  const void* pix[8]; int nsrc, rows_per_src; long long pix_bs, pix_ls; int heads_total, k_head0, v_head0;
+  const unsigned int* tick; const unsigned int* wait_site; int self_rank;
+} ab_attn_segs_args;
+int ab_flash_attn_segs(const ab_attn_segs_args* args, void* stream);
 /* ---- K8: temporal self-attention of the video UNets (csrc/temporal_attn.cu) -----------------------------
  * q/k/v/out are channels-last video tensors [B, F_s, HW, heads*D] (token rows of `row_stride` elements, so q, k, v
  * may be column slices of one fused QKV projection). Every pixel attends over its F frames. With nsrc > 1 the
