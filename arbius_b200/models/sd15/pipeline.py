@@ -149,6 +149,46 @@ class SD15Pipeline:
         self.d2h_bytes = out.size
         return out
 
+    @torch.no_grad()
+    def generate_batch_eager(self, tasks: List[dict], channels_last: bool = False) -> np.ndarray:
+        """The stock-library path at an equal task batch: n tasks as ONE UNet batch of 2n ([n negative prompts, n
+        prompts]), so the comparator in bench.py gets the same batching the native engine uses. ``channels_last``
+        converts the conv weights and activations to NHWC once (cuDNN's tensor-core layout); with
+        ``torch.backends.cudnn.benchmark`` set by the caller this is the strongest eager configuration."""
+        assert self.backend == "eager"
+        dev, dt = self.device, self.dtype
+        a = tasks[0]
+        n = len(tasks)
+        h, w = a["height"] // self.vae_scale, a["width"] // self.vae_scale
+        sch = make_scheduler(a["scheduler"])
+        sch.set_timesteps(a["num_inference_steps"])
+        g = a["guidance_scale"]
+        mf = torch.channels_last if channels_last else torch.contiguous_format
+        if channels_last and not getattr(self, "_cl", False):
+            self.unet.to(memory_format=torch.channels_last)
+            self.vae.to(memory_format=torch.channels_last)
+            self._cl = True
+        ids = torch.cat([torch.stack([self._token_ids(t["prompt"], t["negative_prompt"])[k] for t in tasks]) for k in (0, 1)])
+        ids_host = ids.pin_memory() if dev.type == "cuda" else ids
+        ids = ids_host.to(dev, non_blocking=True)
+        self.h2d_bytes = ids.numel() * 8
+        ctx = self.clip(ids)
+        x = torch.cat([self._noise((1, h, w, 4), t["seed"], NOISE_STREAM_INIT) for t in tasks]).float() * sch.init_noise_sigma
+        bufs: Dict[str, torch.Tensor] = {"x": x}
+        for i, t in enumerate(sch.timesteps):
+            xin = (bufs["x"] * float(np.float32(sch.input_scale(i)))).to(dt).permute(0, 3, 1, 2).repeat(2, 1, 1, 1)
+            tt = torch.full((2 * n,), t, device=dev, dtype=torch.float32)
+            e = self.unet(xin.contiguous(memory_format=mf), tt, ctx).permute(0, 2, 3, 1).float()
+            bufs["eps"] = e[:n] + float(np.float32(g)) * (e[n:] - e[:n])
+            if sch.stochastic:
+                bufs["noise"] = torch.cat([self._noise((1, h, w, 4), tk["seed"], 1 + i) for tk in tasks]).float()
+            apply_plan_torch(sch.plan(i), bufs)
+        img = self.vae(bufs["x"].to(dt).permute(0, 3, 1, 2).contiguous(memory_format=mf)).permute(0, 2, 3, 1)
+        u8 = ((img.float() / 2 + 0.5).clamp(0, 1) * 255).round().to(torch.uint8)
+        out = u8.cpu().numpy()
+        self.d2h_bytes = out.size
+        return out
+
     # ---------------- native ----------------
     def _run_native(self, st: dict, sch: Scheduler, g: float) -> None:
         """Everything between 'ids are on the device' and 'uint8 pixels are on the device', for the ``nb`` tasks of this
