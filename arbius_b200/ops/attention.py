@@ -33,5 +33,9 @@ def flash_attn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, scale: Opti
     a.scale = float(scale) if scale is not None else 0.0
     a.causal = int(causal) | (2 if long_queries else 0)
     a.dtype = native.dtype_code(q.dtype)
+    import sys
+    _g = sys.modules["arbius_b200.ops.gemm"]
+    if _g.RECORD is not None:
+        _g.RECORD.append(f"attn:{b}:{h}:{lq}:{lk}:{d}")
     native.check(lib.ab_flash_attn(C.byref(a), native.stream_ptr()), "ab_flash_attn")
     return out

@@ -120,6 +120,10 @@ def flash_attn_segs(q: torch.Tensor, prefix: Optional[torch.Tensor], pix_ptrs: S
     if sync is not None:
         a.tick, a.wait_site = sync
     a.self_rank = self_rank
+    import sys
+    _g = sys.modules["arbius_b200.ops.gemm"]
+    if _g.RECORD is not None:
+        _g.RECORD.append(f"attn:{b}:{h}:{lq}:{(prefix.shape[1] if prefix is not None else 0) + rows_per_src * len(pix_ptrs)}:{d}")
     native.check(lib.ab_flash_attn_segs(C.byref(a), native.stream_ptr()), "ab_flash_attn_segs")
     return out
 
