@@ -176,7 +176,7 @@ class _KRes:
             lo, hi = max(rk * hl - 1, 0), min((rk + 1) * hl + 1, H)
             hb[:, lo - (rk * hl - 1):lo - (rk * hl - 1) + (hi - lo)].copy_(hf[:, lo:hi])
             xb = xf[:, rk * hl:(rk + 1) * hl].contiguous()
-            with scale_of(P):
+            with scale_of(P, retile=True):
                 h = ops.conv3x3(hb, self.c1w, self.c1b, halo=True)
                 return self._patch_tail(ctx, st, h, xb, None, sc_, sh_), True
         hl, W = x.shape[1], x.shape[2]
@@ -190,7 +190,7 @@ class _KRes:
                     extra.avgpool2x(y[i:i + 1], out=he.interior(i).unsqueeze(0))
                 he.push()
                 xb = extra.avgpool2x(x)
-                with scale_of(P):
+                with scale_of(P, retile=True):
                     h = ops.conv3x3(he.buf, self.c1w, self.c1b, halo=True, sync=ctx.conv_sync(he.site))
                     return self._patch_tail(ctx, st, h, xb, None, sc_, sh_), True
             # the level below does not split: gather the whole tensors on every rank and go on as one GPU would
@@ -215,12 +215,12 @@ class _KRes:
                 ops.upsample_nearest2x(y[i:i + 1], out=he.interior(i).unsqueeze(0))
             he.push()
             xb = ops.upsample_nearest2x(x)
-            with scale_of(P):
+            with scale_of(P, retile=True):
                 h = ops.conv3x3(he.buf, self.c1w, self.c1b, halo=True, sync=ctx.conv_sync(he.site))
                 return self._patch_tail(ctx, st, h, xb, None, sc_, sh_), True
         g1 = st.get("g1") or st.setdefault("g1", pp.PatchGroupNorm(ctx, b, hl, W, cin, self.groups, halo=True))
         yb = g1(x, *self.n1, 1e-5, "silu", x2=x2)
-        with scale_of(P):
+        with scale_of(P, retile=True):
             h = ops.conv3x3(yb, self.c1w, self.c1b, halo=True, sync=ctx.conv_sync(g1.done))
             return self._patch_tail(ctx, st, h, x, x2, sc_, sh_), True
 
@@ -275,8 +275,13 @@ class _KAttn:
         return ops.gemm(a.view(b * l, c), self.wo, self.bo, residual=x.view(b * l, c)).view(b, hh, ww, c)
 
     def patch(self, ctx, x: torch.Tensor, sharded: bool):
-        """Row-band form: the band's fused QKV projection lands in the peer heap, a flag follows it, and the attention
-        kernel fetches every KV tile from the GPU that owns it (waiting for that GPU's flag before its first load)."""
+        """Row-band form. Every rank keeps all bands' fused projections in a local [P, B, ll, 3C] buffer: its own band is
+        written there by the QKV GEMM, and one copy kernel pushes the band's K and V columns into the same slot on every
+        peer and publishes a flag behind them. The attention kernel walks the canonical KV tiles over the P slots and
+        waits for a band's flag before its first load from that slot. Each K/V byte crosses NVLink once per peer; pulling
+        tiles from the owner inside the attention kernel instead (the kernel takes peer addresses as well) moved every
+        remote tile once per query tile of a head — 32 MB instead of 3.5 MB per call at 48x48 on two GPUs, measured as
+        no speed-up at all (profiles/patch_parallel_p2_kernel_table_v0.log)."""
         from ...parallel import patch as pp
         if not sharded:
             with ops.batch_scale(1):
@@ -288,15 +293,18 @@ class _KAttn:
         st = self.__dict__.setdefault("_pp", {}).setdefault(tuple(x.shape), {})
         if "gn" not in st:
             st["gn"] = pp.PatchGroupNorm(ctx, b, hl, ww, c, self.groups, halo=False)
-            st["pix"], st["pix_off"] = ctx.heap.alloc((b, ll, 3 * c), x.dtype)
+            st["pix"], st["pix_off"] = ctx.heap.alloc((P, b, ll, 3 * c), x.dtype)
             st["site"] = ctx.site()
         n = st["gn"](x, *self.norm, 1e-5, None).view(b * ll, c)
-        pix = st["pix"]
-        with ops.batch_scale(P):
+        pix = st["pix"][rk]
+        esz = x.element_size()
+        with ops.batch_scale(P, retile=True):
             ops.gemm(n, self.wqkv, self.bqkv, out=pix.view(b * ll, 3 * c), splitk=1)
-            ctx.signal(st["site"])
+            slot = st["pix_off"] + rk * b * ll * 3 * c * esz + c * esz           # K|V columns of this band's slot
+            ctx.copy([(ctx.heap.peer_ptr(r, slot), pix.data_ptr() + c * esz, 3 * c * esz, 3 * c * esz, 2 * c * esz, b * ll)
+                      for r in range(P) if r != rk], signal=(st["site"], list(range(P))))
             q = pix[:, :, :c].view(b, ll, h, d)
-            srcs = [ctx.heap.peer_ptr(r, st["pix_off"]) for r in range(P)]
+            srcs = [st["pix"][r].data_ptr() for r in range(P)]
             a = pp.flash_attn_segs(q, self.enc_kv[self.off:self.off + b].view(b, t, 3 * h, d), srcs, ll, 3 * c,
                                    ll * 3 * c, h, d, k_head0=h, v_head0=2 * h, heads_total=3 * h, prefix_k_head0=h,
                                    prefix_v_head0=2 * h, self_rank=rk,

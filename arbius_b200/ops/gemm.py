@@ -42,14 +42,17 @@ def get_batch_scale():
 
 
 @contextlib.contextmanager
-def batch_scale(value):
-    """``with batch_scale(v):`` — the canonical-batch multiplier for the GEMM/conv calls of THIS thread."""
-    prev = get_batch_scale()
-    _scale_tls.value = value
+def batch_scale(value, retile: bool = False):
+    """``with batch_scale(v):`` — the canonical-batch multiplier for the GEMM/conv calls of THIS thread.
+    ``retile``: the calls hold 1/v of the canonical rows for good (row bands of patch parallelism), so the tile WIDTH —
+    which never changes a sum's order — is chosen for the rows really present instead of the canonical shape's tuned
+    width (a band needs narrower tiles to fill the SMs); split-K stays the canonical shape's."""
+    prev = get_batch_scale(), getattr(_scale_tls, "retile", False)
+    _scale_tls.value, _scale_tls.retile = value, retile
     try:
         yield
     finally:
-        _scale_tls.value = prev
+        _scale_tls.value, _scale_tls.retile = prev
 
 
 def _canon(m: int) -> int:
@@ -61,6 +64,9 @@ def _tuned_pair(key: str, actual_key: str):
     canonical shape's entry; the tile width is free, so a batch of several tasks takes the entry of its real shape if
     there is one and otherwise lets the library size the tile for the rows it really has (block_n 0)."""
     cfg = tuned_config(key)
+    if cfg is not None and getattr(_scale_tls, "retile", False) and key != actual_key:
+        own = tuned_config(actual_key)
+        return (own[0] if own is not None else 0, cfg[1])
     if cfg is None or get_batch_scale() >= 1 or key == actual_key or _BATCH_BN == "canon":
         return cfg
     own = tuned_config(actual_key)
@@ -189,7 +195,7 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
             rowbias: Optional[torch.Tensor] = None, act: Optional[str] = None, out_scale: float = 1.0,
             splitk: int = 0, block_n: int = 0, halo: bool = False, sync=None) -> torch.Tensor:
     """3x3 / pad 1 / stride 1 implicit-GEMM conv. x [B,H,W,C1] (+ x2 [B,H,W,C2]), w_packed [Cout, 9*(C1+C2)].
-    ``sync``: (tick_ptr, site_ptr, mask) — the kernel's TMA producer waits for those ranks' flags before its first load
+    ``sync``: (tick_ptr, site_ptr, mask, top_mask) — the kernel's TMA producer waits for those ranks' flags before its first load
     (the neighbours push their edge rows straight into this buffer's halo rows; parallel/patch.py).
     ``halo``: x (and x2) are [B, H + 2, W, C] — a row band of the image with the neighbouring bands' edge rows (or zeros
     at the image's top and bottom) in rows 0 and H+1, as a patch-parallel rank holds it; ``batch_scale`` then counts
@@ -210,7 +216,7 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     a.conv, a.nimg, a.H, a.W = 1, b, h, wd
     a.halo = 1 if halo else 0
     if sync is not None:
-        a.sync_tick, a.sync_wait, a.sync_wait_mask = sync
+        a.sync_tick, a.sync_wait, a.sync_wait_mask, a.sync_top_mask = sync
     a.act, a.geglu, a.out_scale = ACT[act], 0, out_scale
     a.dtype = native.dtype_code(x.dtype)
     a.block_n = block_n
@@ -219,7 +225,7 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     key = f"conv:{b}x{_canon(h)}x{wd}:{n}:{c1 + c2}" if halo else f"conv:{_canon(b)}x{h}x{wd}:{n}:{c1 + c2}"
     if RECORD is not None:
         RECORD.append(key)
-    cfg = _tuned_pair(key, key if halo else f"conv:{b}x{h}x{wd}:{n}:{c1 + c2}") if (splitk == 0 and block_n == 0) else None
+    cfg = _tuned_pair(key, f"conv:{b}x{h}x{wd}:{n}:{c1 + c2}") if (splitk == 0 and block_n == 0) else None
     if cfg is not None:
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:

@@ -41,7 +41,7 @@ class GemmArgs(C.Structure):
         ("ldr", C.c_int),
         ("ldrb", C.c_int),
         ("halo", C.c_int),
-        ("sync_tick", C.c_void_p), ("sync_wait", C.c_void_p), ("sync_wait_mask", C.c_uint),
+        ("sync_tick", C.c_void_p), ("sync_wait", C.c_void_p), ("sync_wait_mask", C.c_uint), ("sync_top_mask", C.c_uint),
     ]
 
 

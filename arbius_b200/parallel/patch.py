@@ -6,9 +6,10 @@ Rank r of a ``PeerHeap`` holds rows [r*H/P, (r+1)*H/P) of every activation of a 
 [B, H/P, W, C]. Three operators cross ranks, each in the canonical order of its single-GPU kernel, so the bytes do not
 depend on P:
 
-  GroupNorm       one launch: partial moments of the local canonical shards are pushed into every peer's array, a flag
-                  follows them; every rank merges all 8 shards in shard order and normalises its rows. The rows at the
-                  band's edges are also stored into the neighbours' halo slots    (csrc/norm.cu gn_patch_kernel)
+  GroupNorm       one launch: partial moments of the local canonical shards are stored into every rank's array as
+                  16-byte entries that carry the step's tick inside (no fence, no separate flag); every rank polls all 8
+                  shards' entries, merges them in shard order and normalises its rows. The rows at the band's edges are
+                  also stored into the neighbours' halo slots                     (csrc/norm.cu gn_patch_kernel)
   3x3 conv        reads a [B, H/P + 2, W, C] buffer whose rows 0 and H/P+1 the neighbours wrote; its TMA producer warp
                   waits for their flag before the first load                      (csrc/gemm_tc.cu, args.halo + sync)
   self-attention  K/V projections stay where they were computed; every rank's attention kernel fetches each KV tile
@@ -54,7 +55,7 @@ class PatchCopyArgs(C.Structure):
 
 class GnPatchArgs(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("part_peers", C.c_void_p * 8), ("tick", C.c_void_p),
-                ("stats_sites", C.c_void_p * 8), ("y_batch_stride", C.c_longlong), ("up_halo", C.c_void_p),
+                ("y_batch_stride", C.c_longlong), ("up_halo", C.c_void_p),
                 ("down_halo", C.c_void_p), ("halo_rows", C.c_int), ("done_sites", C.c_void_p * 8),
                 ("done_local", C.c_void_p), ("dry", C.c_int)]
 
@@ -188,7 +189,7 @@ class PatchContext:
         """``sync=`` argument of ops.conv3x3: wait for the neighbours' halo rows inside the conv kernel."""
         if self.dry or not self.nb_mask:
             return None
-        return (self.tick_ptr, site.local, self.nb_mask)
+        return (self.tick_ptr, site.local, self.nb_mask, 0 if self.up is None else 1 << self.up)
 
     def copy(self, segs: List[Tuple[int, int, int, int, int, int]], wait: Optional[Tuple[Site, int]] = None,
              signal: Optional[Tuple[Site, Sequence[int]]] = None) -> None:
@@ -228,7 +229,6 @@ class PatchGroupNorm:
         heap = ctx.heap
         nbytes = b * GN_SHARDS * _GN_MAX_SUB * max(groups, 32) * 16
         self.part, self.part_off = heap.alloc((nbytes,), torch.uint8)
-        self.stats = ctx.site()
         self.halo = halo
         self.done = ctx.site() if (halo or done_to_all) else None
         self.done_to_all = done_to_all
@@ -251,7 +251,6 @@ class PatchGroupNorm:
         a = GroupNormArgs()
         a.x, a.x2 = x.data_ptr(), native.ptr(x2)
         a.gamma, a.beta = native.ptr(gamma), native.ptr(beta)
-        a.partials = ops.norm._gn_workspace(n, self.groups, x.device).data_ptr()
         a.n, a.hw, a.c1, a.c2, a.groups = n, rows, c1, c2, self.groups
         a.eps, a.act, a.dtype = eps, ACT[act], native.dtype_code(x.dtype)
         a.scale, a.shift = native.ptr(scale), native.ptr(shift)
@@ -261,7 +260,6 @@ class PatchGroupNorm:
         pa.world, pa.rank, pa.tick, pa.dry = ctx.world, ctx.rank, ctx.tick_ptr, int(ctx.dry)
         for r in range(ctx.world):
             pa.part_peers[r] = heap.peer_ptr(r, self.part_off)
-            pa.stats_sites[r] = self.stats.peers[r]
         row_b = self.w * self.c * ctx.esz
         if self.halo:
             y = self.buf

@@ -66,6 +66,7 @@ struct GemmParams {
     const unsigned int* sync_tick;
     const unsigned int* sync_wait;
     unsigned int sync_wait_mask;
+    unsigned int sync_top_mask;   // the ranks (of sync_wait_mask) whose rows fill the TOP halo row; the others fill the bottom
     alignas(64) CUtensorMap amaps[8];
     alignas(64) CUtensorMap omap;
 };
@@ -249,8 +250,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // ================= TMA producer =================
         if (lane == 0) {
             if (p.sync_wait) {
-                sync_wait_flags(p.sync_wait, p.sync_wait_mask, *p.sync_tick);
-                fence_proxy_async_all();      // the peers' plain stores (acquired above) before this thread's TMA reads
+                // only a tile that touches a halo row has to wait for the neighbour that fills it: interior tiles start
+                // at once and hide the hand-off's NVLink latency
+                unsigned int need = p.sync_wait_mask;
+                if (p.conv && p.halo) {
+                    need = 0;
+#pragma unroll
+                    for (int s = 0; s < MT; ++s) {
+                        if (h0s[s] == 0) need |= p.sync_wait_mask & p.sync_top_mask;
+                        if (h0s[s] + (1 << p.bh_log2) >= p.H) need |= p.sync_wait_mask & ~p.sync_top_mask;
+                    }
+                }
+                if (need) {
+                    sync_wait_flags(p.sync_wait, need, *p.sync_tick);
+                    fence_proxy_async_all();  // the peers' plain stores (acquired above) before this thread's TMA reads
+                }
             }
             int stage = 0;
             uint32_t phase = 0;
@@ -644,6 +658,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     p.workspace = reinterpret_cast<float*>(a->workspace);
     p.dbg = g_gemm_dbg;
     p.sync_tick = a->sync_tick; p.sync_wait = a->sync_wait; p.sync_wait_mask = a->sync_wait_mask;
+    p.sync_top_mask = a->sync_top_mask;
     AB_REQUIRE(!a->sync_wait || a->sync_tick, "sync_wait needs sync_tick");
     p.M = a->M; p.N = a->N; p.Nout = a->geglu ? a->N / 2 : a->N;
     p.taps = a->conv == 2 ? 3 : (a->conv ? 9 : 1);

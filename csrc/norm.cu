@@ -538,16 +538,18 @@ __global__ void __launch_bounds__(GN_THREADS) gn_fused_kernel(const GnParams p, 
 
 // ---- patch-parallel GroupNorm: statistics, the exchange between the GPUs, and apply in ONE launch ----------------
 // One image's rows are spread over `world` GPUs in row bands; this GPU holds canonical shards
-// [shard_base, shard_base + ns_local). Phase 1 is gn_fused_kernel's (same items, same arithmetic), and every item's
-// moments are also stored into each peer's partial array. After a local grid barrier CTA 0 publishes the tick to every
-// peer; every CTA then waits until all peers' ticks have arrived in this GPU's copy of the site — the peers' moments
-// were stored before their ticks — merges the 8 shards in canonical order and normalises its rows. Rows at the band's
-// edges are additionally stored into the neighbours' halo slots, and the last CTA to finish publishes "rows written":
-// the consumer (the next conv's TMA producer warp, or a gather) waits on that. No barrier kernel on either side.
+// [shard_base, shard_base + ns_local). Phase 1 is gn_fused_kernel's (same items, same arithmetic). Every item's moments
+// then go to EVERY GPU's array (its own included) as self-validating 16-byte entries {mean, tick, M2, tick}: the flag
+// travels inside the data (each 8-byte half carries the tick, so a torn 16-byte store cannot pass), which removes the
+// fence + flag hop of a separate publish and the local grid barrier — a consumer simply polls the entries it needs
+// until they carry this step's tick. The count of an entry is a function of the shapes alone and is recomputed by the
+// reader with the writer's expression, so the merged statistics are bit-identical to the undivided kernel's.
+// Phase 2/3: merge the 8 shards in canonical order, normalise the local rows; rows at the band's edges are also stored
+// into the neighbours' halo slots, and the last CTA to finish publishes "rows written" (a separate flag: the halo rows
+// are too large to carry their own) — the next conv's TMA producer warp, or a gather, waits on that.
 struct GnPatch {
-    float4* part_peers[8];
+    uint4* part_peers[8];
     const unsigned int* tick;
-    unsigned int* stats_sites[8];
     void* up_halo; void* down_halo;
     int halo_rows;
     unsigned int* done_sites[8];
@@ -555,12 +557,37 @@ struct GnPatch {
     int world, rank, dry;
 };
 
+__device__ __forceinline__ void st_ll16(uint4* p, uint4 v) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_ll16(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+// poll one entry until both halves carry `tick` (bounded: a dead peer traps after ~60 s instead of hanging the box)
+__device__ __forceinline__ uint4 gn_poll_entry(const uint4* p, unsigned int tick, bool dry) {
+    uint4 v = ld_ll16(p);
+    if (dry || (v.y == tick && v.w == tick)) return v;
+    const long long t0 = clock64();
+    for (;;) {
+        v = ld_ll16(p);
+        if (v.y == tick && v.w == tick) return v;
+        __nanosleep(20);
+        if (clock64() - t0 > 120000000000LL) {
+            printf("gn_patch: moments entry never arrived (tick %u, have %u/%u) block %d\n", tick, v.y, v.w, blockIdx.x);
+            __trap();
+        }
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, const __grid_constant__ GnPatch x,
-                                                              unsigned int* bar, int cache_rows) {
+                                                              int cache_rows) {
     extern __shared__ __align__(16) unsigned char gn_smem[];
     __shared__ GnMoments shard_mom[GN_SHARDS][GN_MAX_GROUPS + 1];
     __shared__ float2 s_stats[GN_MAX_GROUPS];
+    __shared__ float4 s_item[GN_MAX_GROUPS];
     const int C = p.c1 + p.c2;
     const int ncol = C / 8;
     const int cpg = C / p.groups;
@@ -574,19 +601,18 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
     const int total_items = p.n * items_per_img;
     const bool use_cache = cache_rows > 0;
     const unsigned int tick = x.tick ? *x.tick : 0u;
+    const int shard_len = p.hw / ns;                       // rows of one canonical shard (hw % ns == 0)
 
     auto item_rows = [&](int item, int& n, int& shard, int& sb, int& r0, int& r1) {
         n = item / items_per_img;
         const int rem = item - n * items_per_img;
         shard = rem / p.sub; sb = rem - shard * p.sub;
-        const int s_begin = static_cast<int>((static_cast<long long>(shard) * p.hw) / ns);
-        const int s_end = static_cast<int>((static_cast<long long>(shard + 1) * p.hw) / ns);
-        const int len = s_end - s_begin;
-        r0 = s_begin + static_cast<int>((static_cast<long long>(sb) * len) / p.sub);
-        r1 = s_begin + static_cast<int>((static_cast<long long>(sb + 1) * len) / p.sub);
+        const int s_begin = shard * shard_len;
+        r0 = s_begin + static_cast<int>((static_cast<long long>(sb) * shard_len) / p.sub);
+        r1 = s_begin + static_cast<int>((static_cast<long long>(sb + 1) * shard_len) / p.sub);
     };
 
-    // ---------------- phase 1: per-item moments (+ keep the rows), pushed to every GPU ----------------
+    // ---------------- phase 1: per-item moments (+ keep the rows), stored to every GPU with the tick inside ----------------
     int cached = 0;
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
         int n, shard, sb, r0, r1;
@@ -645,14 +671,14 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
             }
         }
         __syncthreads();
-        const long long pidx = ((static_cast<long long>(n) * GN_SHARDS + p.shard_base + shard) * p.sub + sb) * p.groups;
-        gn_block_moments(s_sum, s_sq, RL, C, cpg, p.groups, r1 - r0, p.partials + pidx);
+        gn_block_moments(s_sum, s_sq, RL, C, cpg, p.groups, r1 - r0, s_item);
         __syncthreads();
+        const long long pidx = ((static_cast<long long>(n) * GN_SHARDS + p.shard_base + shard) * p.sub + sb) * p.groups;
         for (int t = threadIdx.x; t < p.groups * x.world; t += GN_THREADS) {
             const int peer = t / p.groups, g = t - peer * p.groups;
-            if (peer != x.rank) x.part_peers[peer][pidx + g] = p.partials[pidx + g];
+            const float4 m = s_item[g];
+            st_ll16(x.part_peers[peer] + pidx + g, make_uint4(__float_as_uint(m.y), tick, __float_as_uint(m.z), tick));
         }
-        __threadfence_system();
         __syncthreads();
         cached += r1 - r0;
     }
@@ -666,21 +692,12 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
         if (beta) h_beta = __ldg(reinterpret_cast<const uint4*>(beta + c_h));
     }
 
-    gn_grid_barrier(bar, gridDim.x);          // every local item's moments are stored here and on every peer
-    if (!x.dry) {
-        if (blockIdx.x == 0 && threadIdx.x < x.world && threadIdx.x != x.rank) {
-            __threadfence_system();
-            st_release_sys_u32(x.stats_sites[threadIdx.x] + x.rank, tick);
-        }
-        if (threadIdx.x < x.world && threadIdx.x != x.rank) sync_wait_flags(x.stats_sites[x.rank], 1u << threadIdx.x, tick);
-        __syncthreads();
-    }
-
-    // ---------------- phase 2 + 3: merge all 8 shards in canonical order, normalise, push the edge rows ----------------
+    // ---------------- phase 2 + 3: poll + merge all 8 shards in canonical order, normalise, push the edge rows ----------------
     const T* scale = reinterpret_cast<const T*>(p.scale);
     const T* shift = reinterpret_cast<const T*>(p.shift);
     const long long y_bs = p.y_bs > 0 ? p.y_bs : static_cast<long long>(p.hw) * C;
     const int lo_edge = x.halo_rows, hi_edge = p.hw - x.halo_rows;
+    const uint4* part_local = x.part_peers[x.rank];
     int stats_n = -1;
     cached = 0;
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
@@ -688,18 +705,16 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
         item_rows(item, n, shard, sb, r0, r1);
         if (n != stats_n) {
             __syncthreads();
-            const float4* part = p.partials + static_cast<long long>(n) * GN_SHARDS * p.sub * p.groups;
+            const uint4* part = part_local + static_cast<long long>(n) * GN_SHARDS * p.sub * p.groups;
             for (int idx = threadIdx.x; idx < GN_SHARDS * p.groups; idx += GN_THREADS) {
                 const int sh = idx / p.groups, g = idx % p.groups;
                 GnMoments acc{0.f, 0.f, 0.f};
-                for (int sb0 = 0; sb0 < p.sub; sb0 += 8) {
-                    float4 q4[8];
-#pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (sb0 + u < p.sub) q4[u] = __ldcg(&part[(sh * p.sub + sb0 + u) * p.groups + g]);
-#pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (sb0 + u < p.sub) acc = gn_merge(acc, GnMoments{q4[u].x, q4[u].y, q4[u].z});
+                for (int sbi = 0; sbi < p.sub; ++sbi) {
+                    const uint4 e = gn_poll_entry(&part[(sh * p.sub + sbi) * p.groups + g], tick, x.dry != 0);
+                    // the writer's count: rows of sub-block sbi of a shard, times channels per group (gn_block_moments)
+                    const int rows = static_cast<int>((static_cast<long long>(sbi + 1) * shard_len) / p.sub) -
+                                     static_cast<int>((static_cast<long long>(sbi) * shard_len) / p.sub);
+                    acc = gn_merge(acc, GnMoments{static_cast<float>(rows) * cpg, __uint_as_float(e.x), __uint_as_float(e.z)});
                 }
                 shard_mom[sh][g] = acc;
             }
@@ -993,7 +1008,7 @@ extern "C" int ab_groupnorm_sharded_apply(const ab_groupnorm_args* a, int world,
 extern "C" int ab_groupnorm_patch(const ab_groupnorm_args* a, const ab_gn_patch_args* pa, void* stream_) {
     using namespace ab;
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-    AB_REQUIRE(a && pa && a->x && a->y && a->partials, "null pointer");
+    AB_REQUIRE(a && pa && a->x && a->y, "null pointer");
     AB_REQUIRE(pa->world == 2 || pa->world == 4 || pa->world == 8, "world must be 2, 4 or 8");
     AB_REQUIRE(pa->rank >= 0 && pa->rank < pa->world, "bad rank");
     const int C = a->c1 + a->c2;
@@ -1006,8 +1021,6 @@ extern "C" int ab_groupnorm_patch(const ab_groupnorm_args* a, const ab_gn_patch_
     AB_REQUIRE(pa->halo_rows >= 0 && pa->halo_rows <= a->hw, "bad halo row count");
     GnParams p{};
     p.x = a->x; p.x2 = a->x2; p.y = a->y; p.gamma = a->gamma; p.beta = a->beta; p.scale = a->scale; p.shift = a->shift;
-    uint8_t* ws = reinterpret_cast<uint8_t*>(a->partials);
-    p.counters = reinterpret_cast<unsigned int*>(ws);
     p.n = a->n; p.hw = a->hw; p.c1 = a->c1; p.c2 = a->c2; p.groups = a->groups;
     p.sub = gn_sub_blocks(a->hw * pa->world);
     p.ns_local = ns; p.shard_base = pa->rank * ns;
@@ -1016,18 +1029,17 @@ extern "C" int ab_groupnorm_patch(const ab_groupnorm_args* a, const ab_gn_patch_
     GnPatch x{};
     for (int r = 0; r < pa->world; ++r) {
         AB_REQUIRE(pa->part_peers[r], "missing partial-moment array");
-        x.part_peers[r] = reinterpret_cast<float4*>(pa->part_peers[r]);
-        AB_REQUIRE(pa->dry || pa->stats_sites[r], "missing stats site");
-        x.stats_sites[r] = pa->stats_sites[r];
+        x.part_peers[r] = reinterpret_cast<uint4*>(pa->part_peers[r]);
         x.done_sites[r] = pa->done_sites[r];
     }
-    p.partials = x.part_peers[pa->rank];
     x.tick = pa->tick; x.up_halo = pa->up_halo; x.down_halo = pa->down_halo; x.halo_rows = pa->halo_rows;
     x.done_local = pa->done_local; x.world = pa->world; x.rank = pa->rank; x.dry = pa->dry;
     const int ncol = C / 8;
     const int RL = ncol >= GN_THREADS ? 1 : GN_THREADS / ncol;
     const size_t smem = static_cast<size_t>(2) * RL * C * sizeof(float);
     AB_REQUIRE(smem <= 48 * 1024, "channel count too large for the stats kernel");
+    // One CTA per SM at most, all co-resident (cooperative launch): a CTA polls for moments that other CTAs of this
+    // grid produce, so none of them may be waiting for an SM.
     const int n_sm = ab_sm_count();
     const int total_items = a->n * ns * p.sub;
     const int grid_f = total_items < n_sm ? total_items : n_sm;
@@ -1039,7 +1051,6 @@ extern "C" int ab_groupnorm_patch(const ab_groupnorm_args* a, const ab_gn_patch_
     if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_patch_kernel<__half>), 200 * 1024)) return -1;
     if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_patch_kernel<__nv_bfloat16>), 200 * 1024)) return -1;
     const size_t smem_f = smem + static_cast<size_t>(cache_rows) * C * 2;
-    unsigned int* bar = p.counters + a->n;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid_f);
     cfg.blockDim = dim3(GN_THREADS);
@@ -1050,8 +1061,8 @@ extern "C" int ab_groupnorm_patch(const ab_groupnorm_args* a, const ab_gn_patch_
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (a->dtype == AB_BF16) AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__nv_bfloat16>, p, x, bar, cache_rows));
-    else AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__half>, p, x, bar, cache_rows));
+    if (a->dtype == AB_BF16) AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__nv_bfloat16>, p, x, cache_rows));
+    else AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__half>, p, x, cache_rows));
     ab_count_launch(1);
     return 0;
 }

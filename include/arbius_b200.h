@@ -73,6 +73,8 @@ typedef struct {
    * producer thread spins until every rank in sync_wait_mask has published *sync_tick in this GPU's copy of the
    * site — the neighbours' halo rows, pushed straight into A's halo slots, have then arrived. NULL = no wait. */
   const unsigned int* sync_tick; const unsigned int* sync_wait; unsigned int sync_wait_mask;
+  unsigned int sync_top_mask;   /* conv + halo: the ranks of sync_wait_mask that fill the TOP halo row (the rest fill the
+                                 * bottom one); only tiles that touch a halo row wait, and only for that neighbour */
 } ab_gemm_args;
 int ab_gemm(const ab_gemm_args* args, void* stream);
 /* Multi-GPU forms of the same kernel (one NVSwitch box; pointers may be peer-mapped addresses).
@@ -151,18 +153,18 @@ typedef struct {
   unsigned int* local_site;
 } ab_patch_copy_args;
 int ab_patch_copy(const ab_patch_copy_args* args, void* stream);
-/* GroupNorm of a row band in ONE launch (patch parallelism): partial moments of this GPU's canonical shards are
- * pushed into every peer's array, the peers' arrive the same way, all are merged in canonical order, the local rows
- * are normalised. y may be the interior of a [n, H+2, W, C] halo buffer (y_batch_stride); with halo_rows > 0 the
- * band's first / last halo_rows rows are also stored into the neighbours' halo slots (up_halo / down_halo: address of
- * sample 0's slot on that GPU, batch stride y_batch_stride) and the last CTA publishes the tick to done_sites (the
- * consumers' wait: the next conv's producer warp). args->hw is the LOCAL row count; args->partials the usual local
- * workspace. Output bytes equal ab_groupnorm on the undivided tensor. dry != 0: no waits, no signals (module warm-up). */
+/* GroupNorm of a row band in ONE launch (patch parallelism): the partial moments of this GPU's canonical shards go to
+ * every GPU's array as self-validating 16-byte entries {mean, tick, M2, tick} (the flag travels inside the data: no
+ * fence, no separate publish, no grid barrier), every GPU polls the entries of all 8 shards, merges them in canonical
+ * order and normalises its rows. y may be the interior of a [n, H+2, W, C] halo buffer (y_batch_stride); with
+ * halo_rows > 0 the band's first / last halo_rows rows are also stored into the neighbours' halo slots (up_halo /
+ * down_halo: address of sample 0's slot on that GPU, batch stride y_batch_stride) and the last CTA publishes the tick
+ * to done_sites (the consumers' wait: the next conv's producer warp). args->hw is the LOCAL row count; args->partials
+ * is not used. Output bytes equal ab_groupnorm on the undivided tensor. dry != 0: no waits, no signals (module warm-up). */
 typedef struct {
   int world, rank;
-  void* part_peers[8];            /* every rank's [n][8][sub][groups] float4 array (peer-mapped; [rank] = local) */
+  void* part_peers[8];            /* every rank's [n][8][sub][groups] x 16 B array (peer-mapped; [rank] = local), zero-filled once */
   const unsigned int* tick;
-  unsigned int* stats_sites[8];   /* the stats site on every rank (peer-mapped; [rank] = local) */
   long long y_batch_stride;       /* elements; 0 = hw * C */
   void* up_halo; void* down_halo; int halo_rows;
   unsigned int* done_sites[8];    /* who gets the "rows written" tick: neighbours (halo) or everyone (gather); NULL = skip */
