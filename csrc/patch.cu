@@ -128,3 +128,60 @@ extern "C" int ab_patch_copy(const ab_patch_copy_args* a, void* stream_) {
     ab_count_launch(1);
     return 0;
 }
+
+// ---- hand-off latency probe (profiles/: the numbers the patch-parallel design is sized by) --------------------------
+// Two GPUs bounce a flag `iters` times. mode 0: flag only (st.release.sys / ld.acquire.sys). mode 1: a 16-byte
+// flag-in-data entry (volatile v4 store / poll). mode 2: `bytes` of plain stores into the peer's buffer by the whole
+// CTA, __threadfence_system, then the flag — the shape of a halo push. One CTA per GPU; rank 0 serves first.
+// out[0] = cycles for all iterations (clock64 of this GPU), out[1] = iterations.
+namespace ab {
+__global__ void __launch_bounds__(256) pingpong_kernel(unsigned int* my_flags, unsigned int* peer_flags, uint4* peer_buf,
+                                                       int rank, int iters, int mode, int bytes, unsigned int base,
+                                                       long long* out) {
+    __shared__ long long t0;
+    if (threadIdx.x == 0) t0 = clock64();
+    __syncthreads();
+    for (int i = 1; i <= iters; ++i) {
+        const unsigned int v = base + static_cast<unsigned int>(i);
+        for (int turn = 0; turn < 2; ++turn) {
+            if (turn == rank) {               // my turn to send
+                if (mode == 2) {
+                    for (int j = threadIdx.x; j < bytes / 16; j += 256) peer_buf[j] = make_uint4(v, v, v, v);
+                    __threadfence_system();
+                    __syncthreads();
+                }
+                if (threadIdx.x == 0) {
+                    if (mode == 1) {
+                        asm volatile("st.volatile.global.v4.u32 [%0], {%1, %1, %1, %1};" ::"l"(peer_flags + 16), "r"(v) : "memory");
+                    } else {
+                        st_release_sys_u32(peer_flags + rank, v);
+                    }
+                }
+            } else {                          // wait for the peer's send
+                if (threadIdx.x == 0) {
+                    if (mode == 1) {
+                        unsigned int a, b, c, d;
+                        do {
+                            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(my_flags + 16) : "memory");
+                        } while (b != v || d != v);
+                    } else {
+                        while (static_cast<int>(ld_acquire_sys_u32(my_flags + (1 - rank)) - v) < 0) {}
+                    }
+                }
+                __syncthreads();
+            }
+        }
+    }
+    if (threadIdx.x == 0) { out[0] = clock64() - t0; out[1] = iters; }
+}
+}  // namespace ab
+
+extern "C" int ab_sync_pingpong(unsigned int* my_flags, unsigned int* peer_flags, void* peer_buf, int rank, int iters,
+                                int mode, int bytes, unsigned int base, long long* out, void* stream_) {
+    AB_REQUIRE(my_flags && peer_flags && out && (rank == 0 || rank == 1) && iters > 0 && bytes % 16 == 0, "bad arguments");
+    ab::pingpong_kernel<<<1, 256, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(my_flags, peer_flags, reinterpret_cast<uint4*>(peer_buf),
+                                                                                 rank, iters, mode, bytes, base, out);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

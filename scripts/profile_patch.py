@@ -66,6 +66,7 @@ def main():
         torch.cuda.synchronize()
     if rank == 0:
         table(p1, f"one GPU, {a.steps} UNet steps, {t_one:.1f} ms per task")
+        p1.export_chrome_trace("gpurun_out/trace_kandinsky_p1.json")
     del one
     torch.cuda.empty_cache()
     heap = PeerHeap(6 << 30)
@@ -85,6 +86,7 @@ def main():
         torch.cuda.synchronize()
     if rank == 0:
         table(p2, f"patch-parallel P={world}, {a.steps} UNet steps, {t_par:.1f} ms per task")
+    p2.export_chrome_trace(f"gpurun_out/trace_kandinsky_patch_p{world}_rank{rank}.json")
     dist.barrier()
     heap.close()
     dist.destroy_process_group()
