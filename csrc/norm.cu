@@ -709,12 +709,22 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
             for (int idx = threadIdx.x; idx < GN_SHARDS * p.groups; idx += GN_THREADS) {
                 const int sh = idx / p.groups, g = idx % p.groups;
                 GnMoments acc{0.f, 0.f, 0.f};
-                for (int sbi = 0; sbi < p.sub; ++sbi) {
-                    const uint4 e = gn_poll_entry(&part[(sh * p.sub + sbi) * p.groups + g], tick, x.dry != 0);
-                    // the writer's count: rows of sub-block sbi of a shard, times channels per group (gn_block_moments)
-                    const int rows = static_cast<int>((static_cast<long long>(sbi + 1) * shard_len) / p.sub) -
-                                     static_cast<int>((static_cast<long long>(sbi) * shard_len) / p.sub);
-                    acc = gn_merge(acc, GnMoments{static_cast<float>(rows) * cpg, __uint_as_float(e.x), __uint_as_float(e.z)});
+                for (int sb0 = 0; sb0 < p.sub; sb0 += 8) {           // eight loads in flight, merged in index order
+                    uint4 e[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (sb0 + u < p.sub) e[u] = ld_ll16(&part[(sh * p.sub + sb0 + u) * p.groups + g]);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        if (sb0 + u >= p.sub) break;
+                        const int sbi = sb0 + u;
+                        if (!x.dry && (e[u].y != tick || e[u].w != tick))
+                            e[u] = gn_poll_entry(&part[(sh * p.sub + sbi) * p.groups + g], tick, false);
+                        // the writer's count: rows of sub-block sbi of a shard, times channels per group (gn_block_moments)
+                        const int rows = static_cast<int>((static_cast<long long>(sbi + 1) * shard_len) / p.sub) -
+                                         static_cast<int>((static_cast<long long>(sbi) * shard_len) / p.sub);
+                        acc = gn_merge(acc, GnMoments{static_cast<float>(rows) * cpg, __uint_as_float(e[u].x), __uint_as_float(e[u].z)});
+                    }
                 }
                 shard_mom[sh][g] = acc;
             }
@@ -787,7 +797,7 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
     if (x.done_local && !x.dry) {
         __syncthreads();
         if (threadIdx.x == 0) {
-            __threadfence_system();
+            __threadfence_system();       // this CTA's rows (and any it stored into a neighbour) before its arrival counts
             const unsigned int ticket = atomicAdd(x.done_local + 8, 1u);
             if (ticket == gridDim.x - 1) {
                 x.done_local[8] = 0;

@@ -52,7 +52,21 @@ __global__ void __launch_bounds__(256) patch_copy_kernel(const __grid_constant__
         const long long total = w16 * g.rows;
         uint4* dst = reinterpret_cast<uint4*>(g.dst);
         const uint4* src = reinterpret_cast<const uint4*>(g.src);
-        for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
+        const long long stride = static_cast<long long>(gridDim.x) * 256;
+        long long i = blockIdx.x * 256LL + threadIdx.x;
+        for (; i + 3 * stride < total; i += 4 * stride) {            // four loads in flight per thread
+            uint4 v[4];
+            long long o[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long j = i + u * stride, r = j / w16, c = j - r * w16;
+                v[u] = src[r * sp + c];
+                o[u] = r * dp + c;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) dst[o[u]] = v[u];
+        }
+        for (; i < total; i += stride) {
             const long long r = i / w16, c = i - r * w16;
             dst[r * dp + c] = src[r * sp + c];
         }
@@ -121,8 +135,9 @@ extern "C" int ab_patch_copy(const ab_patch_copy_args* a, void* stream_) {
     p.nseg = a->nseg; p.tick = a->tick; p.wait_site = a->wait_site; p.wait_mask = a->wait_mask;
     for (int d = 0; d < 8; ++d) p.signal_sites[d] = d < a->world ? a->signal_sites[d] : nullptr;
     p.world = a->world; p.rank = a->rank; p.local_site = a->local_site;
-    long long blocks = total / (256 * 4) + 1;
-    if (blocks > 148 * 4) blocks = 148 * 4;
+    // 16 x 16 bytes per thread: enough CTAs to keep NVLink busy, few enough that the arrival count stays short
+    long long blocks = total / (256 * 16) + 1;
+    if (blocks > 148) blocks = 148;
     patch_copy_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(p);
     AB_CHECK_CUDA(cudaGetLastError());
     ab_count_launch(1);

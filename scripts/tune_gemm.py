@@ -125,8 +125,65 @@ def tune_batched(a):
     json.dump(out, open(a.out.replace(".json", f"_tb{a.task_batch}.json"), "w"), indent=0, sort_keys=True)
 
 
+def tune_kandinsky(a):
+    """Kandinsky 2.1's UNet shapes: (block_n, splitk) for every recorded shape of the undivided task — this FIXES the
+    canonical split-K of those shapes — and then, for the row bands of patch parallelism (1/P of the rows, P in
+    --bands), the best tile width alone with split-K held at the canonical shape's. Writes the merged table."""
+    from arbius_b200.models.kandinsky.pipeline import Kandinsky2Config, Kandinsky2Pipeline
+    cfg = Kandinsky2Config()
+    cfg.steps, cfg.prior_steps = 1, 1
+    pipe = Kandinsky2Pipeline(cfg, backend="native", device="cuda", dtype=torch.float16, use_graph=False)
+    G.RECORD = []
+    pipe.generate("cat", 768, 768, seed=1)
+    torch.cuda.synchronize()
+    counts = Counter(k for k in G.RECORD if k.split(":")[0] in ("lin", "geglu", "conv"))
+    G.RECORD = None
+    del pipe
+    torch.cuda.empty_cache()
+    table = json.load(open("arbius_b200/ops/tuned_sm100.json"))
+    new, report = {}, []
+    for key, cnt in sorted(counts.items(), key=lambda kv: -kv[1]):
+        parts = key.split(":")
+        if parts[0] == "conv":
+            b_, h, w = (int(v) for v in parts[1].split("x"))
+            m = b_ * h * w
+        else:
+            m = int(parts[1])
+        if m < 256 or key in table:
+            continue                                   # tiny per-task GEMMs (embeddings, prior): the heuristic is fine
+        res, flops, _ = bench_key(key)
+        (bn, sk), us = min(res.items(), key=lambda kv: kv[1])
+        new[key] = [bn, sk]
+        report.append(dict(key=key, calls=cnt, best=[bn, sk], us=round(us, 2), tflops=round(flops / us / 1e6, 1),
+                           all={f"{b2}/{s2}": round(v, 2) for (b2, s2), v in sorted(res.items())}))
+        print(json.dumps({k: v for k, v in report[-1].items() if k != "all"}), flush=True)
+        for P in a.bands:
+            if parts[0] == "conv":
+                if h % 8 or ((h // 8) * w) % 8 or h % P:
+                    continue
+                band = f"conv:{b_}x{h // P}x{w}:{parts[2]}:{parts[3]}"
+            else:
+                if m % (P * 8):
+                    continue
+                band = f"{parts[0]}:{m // P}:{parts[2]}:{parts[3]}"
+            if band in table or band in new:
+                continue
+            r2, f2, _ = bench_key(band, only_splitk=sk)
+            (bn2, _), us2 = min(r2.items(), key=lambda kv: kv[1])
+            new[band] = [bn2, sk]
+            report.append(dict(key=band, band_of=key, P=P, best=[bn2, sk], us=round(us2, 2), tflops=round(f2 / us2 / 1e6, 1),
+                               all={f"{b2}/{s2}": round(v, 2) for (b2, s2), v in sorted(r2.items())}))
+            print(json.dumps({k: v for k, v in report[-1].items() if k != "all"}), flush=True)
+    table.update(new)
+    json.dump(report, open(a.out.replace(".json", "_kandinsky.json"), "w"), indent=1)
+    json.dump(table, open("gpurun_out/tuned_sm100.json", "w"), indent=0, sort_keys=True)
+    print(f"tuned {len(new)} shapes; merged table in gpurun_out/tuned_sm100.json", flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "kandinsky2"])
+    ap.add_argument("--bands", type=lambda v: [int(x) for x in v.split(",")], default=[2, 4, 8])
     ap.add_argument("--write", action="store_true")
     ap.add_argument("--out", default="gpurun_out/tune_report.json")
     ap.add_argument("--size", type=int, default=512)
@@ -136,6 +193,8 @@ def main():
     a = ap.parse_args()
     if a.task_batch > 1:
         return tune_batched(a)
+    if a.model == "kandinsky2":
+        return tune_kandinsky(a)
     from arbius_b200.models.sd15.pipeline import SD15Config, SD15Pipeline
     pipe = SD15Pipeline(SD15Config(), backend="native", device="cuda", dtype=torch.float16, use_graph=False)
     G.RECORD = []
