@@ -63,7 +63,8 @@ class Kandinsky2Pipeline:
             assert backend == "native" and cfg_parallel is None
             from ...parallel.patch import PatchContext
             self.pp = PatchContext(patch_parallel, dtype)
-        self.tokenizer = HashTokenizer(cfg.text.vocab_size, 77)
+        from ..tokenizer import load_xlmr_tokenizer
+        self.tokenizer = load_xlmr_tokenizer(model_dir, cfg.text.vocab_size, 77)
         with torch.device(device):
             unet, prior = KandinskyUNet(cfg.unet), DiffusionPrior(cfg.prior, text_dim=cfg.text.hidden)
             text, movq = TextEncoderXLMR(cfg.text), MoVQDecoder(cfg.movq)
@@ -71,9 +72,22 @@ class Kandinsky2Pipeline:
         if model_dir:
             from pathlib import Path
             ck = Path(model_dir)
+            from . import keymap
             for mod, name in zip(mods, ("decoder_fp16.ckpt", "prior_fp16.ckpt", "text_encoder.ckpt", "movq_final.ckpt")):
                 sd = torch.load(ck / name, map_location="cpu", weights_only=True)
-                mod.load_state_dict(sd.get("state_dict", sd), strict=True)
+                sd = sd.get("state_dict", sd)
+                # the files of kasumi-1/Kandinsky-2 carry upstream names and per-head interleaved attention projections
+                # (keymap.py); files saved from these modules load as they are
+                if name.startswith("decoder") and not sd.get("__arbius_layout__"):
+                    sd = keymap.map_unet(sd, cfg.unet.head_dim)
+                elif name.startswith("prior") and keymap.is_upstream_prior(sd):
+                    sd = keymap.map_prior(sd, cfg.prior.heads)
+                elif name.startswith("text_encoder") and keymap.is_upstream_text_encoder(sd):
+                    sd = keymap.map_text_encoder(sd, cfg.text.max_positions)
+                elif name.startswith("movq") and keymap.is_upstream_movq(sd):
+                    sd = keymap.map_movq(sd, len(cfg.movq.ch_mult))
+                sd.pop("__arbius_layout__", None)
+                mod.load_state_dict(sd, strict=True)
         else:
             for i, m in enumerate(mods):
                 init_weights_(m, seed + 20 + i)

@@ -90,6 +90,37 @@ class HashTokenizer:
         return out + [self.eos] * (self.max_len - len(out))
 
 
+class XlmrTokenizer:
+    """XLM-RoBERTa tokenizer of Kandinsky 2.1's MultilingualCLIP text encoder: the upstream ``sentencepiece.bpe.model``
+    run by the SentencePiece library, with fairseq's id layout on top — <s> 0, <pad> 1, </s> 2, <unk> 3, every piece id
+    shifted by one — framed as <s> pieces </s> and padded with <pad> to 77 (reference: the container behind
+    templates/kandinsky2.json tokenises with ``max_length=77, padding='max_length', truncation=True``)."""
+    BOS, PAD, EOS, UNK = 0, 1, 2, 3
+
+    def __init__(self, model_file: str | Path, max_len: int = MAX_LEN):
+        import sentencepiece as spm
+        self.sp = spm.SentencePieceProcessor(model_file=str(model_file))
+        self.max_len = max_len
+        self.vocab_size = self.sp.get_piece_size() + 2          # + the fairseq offset and <mask>
+        self.bos, self.eos = self.BOS, self.EOS
+
+    def encode(self, text: str) -> List[int]:
+        ids = [self.UNK if i == self.sp.unk_id() else i + 1 for i in self.sp.encode(text)]
+        ids = ids[: self.max_len - 2]
+        out = [self.BOS] + ids + [self.EOS]
+        return out + [self.PAD] * (self.max_len - len(out))
+
+
+def load_xlmr_tokenizer(model_dir: Optional[str | Path], vocab_size: int, max_len: int = MAX_LEN):
+    """``sentencepiece.bpe.model`` next to the checkpoints (or under ``text_encoder/``), else the hash stand-in."""
+    if model_dir is not None:
+        d = Path(model_dir)
+        for cand in (d / "sentencepiece.bpe.model", d / "text_encoder" / "sentencepiece.bpe.model"):
+            if cand.exists():
+                return XlmrTokenizer(cand, max_len)
+    return HashTokenizer(vocab_size, max_len)
+
+
 def load_tokenizer(model_dir: Optional[str | Path] = None, vocab_size: int = 49408):
     if model_dir is not None:
         d = Path(model_dir)

@@ -61,6 +61,7 @@ struct GemmParams {
     // scattered over 32 rows per warp instruction. Off for GEGLU, split-K partials and reduce-scatter.
     int tma_store;
     int mt;                     // 128-row M tiles per CTA (1 or 2)
+    int deep;                   // one CTA per SM at most: use the deep-pipeline instantiation (see launch_gemm)
     // cross-GPU hand-off folded into the kernel (patch parallelism): the producer thread waits for the ranks in
     // sync_wait_mask to publish *sync_tick in this GPU's copy of the site before its first load (halo rows arrived)
     const unsigned int* sync_tick;
@@ -579,11 +580,22 @@ static int launch_gemm_mt(const CUtensorMap& tmA, const CUtensorMap& tmA2, const
 // STAGES is the depth for one 128-row tile per CTA; the two-tile variant exists for BN = 256 only (three 64 KB stages).
 // At BN <= 160 two co-resident CTAs already overlap each other's epilogue and loads: the ZeroScope convs measured
 // 1137-1236 TFLOP/s with one tile per CTA and 1121-1238 with two, so those widths keep one.
+// Deep-pipeline variants. When a launch has no more CTAs than the GPU has SMs (the low-resolution UNet levels, a row band
+// of patch parallelism), each SM holds ONE CTA and its main loop is a serial chain of K steps whose rate is
+// stages / (TMA round trip): with 3-4 stages a 128 x 64 step took ~0.35 us whatever the tile width (tuner, Kandinsky
+// 48x48x768 conv: 48.9 us on one GPU, still 38.2 us with an eighth of the rows). A lone CTA can have all 227 KB, so these
+// instantiations keep ~190 KB of operands in flight (10 / 8 / 7 / 6 / 5 stages). Same MMA order, same bytes. Only the
+// plain epilogue is instantiated (convs, QKV / output projections): the latency-bound layers have no activation.
+template <int BN> struct DeepStages { static constexpr int value = BN <= 32 ? 10 : BN <= 64 ? 8 : BN <= 96 ? 7 : BN <= 128 ? 6 : 5; };
+
 template <int BN, int STAGES, typename T, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
                        dim3 grid, cudaStream_t stream) {
     if constexpr (BN == 256) {
         if (p.mt == 2) return launch_gemm_mt<BN, 3, T, EPI, 2>(tmA, tmA2, tmB, p, grid, stream);
+    }
+    if constexpr (BN <= 160 && EPI == EPI_NONE) {
+        if (p.deep) return launch_gemm_mt<BN, DeepStages<BN>::value, T, EPI, 1>(tmA, tmA2, tmB, p, grid, stream);
     }
     return launch_gemm_mt<BN, STAGES, T, EPI, 1>(tmA, tmA2, tmB, p, grid, stream);
 }
@@ -790,6 +802,9 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     p.mt = (mt_on && !ag && bn == 256 && tiles_m % 2 == 0 && p.chunks_per_split >= 24 &&
             static_cast<long long>(tiles_m / 2) * n_tiles * grid_z >= 2LL * ab_sm_count()) ? 2 : 1;
     dim3 grid(tiles_m / p.mt, n_tiles, grid_z);
+    static const bool deep_on = [] { const char* e = getenv("AB_GEMM_DEEP"); return !(e && e[0] == '0'); }();
+    p.deep = (deep_on && p.mt == 1 && static_cast<long long>(grid.x) * grid.y * grid.z <= ab_sm_count() &&
+              p.chunks_per_split >= 12) ? 1 : 0;
     int epi = a->geglu ? EPI_GEGLU
             : a->act == ACT_NONE ? EPI_NONE
             : a->act == ACT_SILU ? EPI_SILU
