@@ -11,7 +11,10 @@ objs=()
 for src in "$here"/*.cu; do
   obj="$out/obj/$(basename "${src%.cu}").o"
   objs+=("$obj")
-  if [[ ! -f "$obj" || "$src" -nt "$obj" || -n "$(find "$here" -name "*.cuh" -newer "$obj")" || "$here/../include/arbius_b200.h" -nt "$obj" ]]; then
+  # gemm_tc_bf16.cu is a three-line wrapper that #includes gemm_tc.cu: it is stale whenever gemm_tc.cu is newer
+  dep="$src"
+  [[ "$(basename "$src")" == "gemm_tc_bf16.cu" ]] && dep="$here/gemm_tc.cu"
+  if [[ ! -f "$obj" || "$src" -nt "$obj" || "$dep" -nt "$obj" || -n "$(find "$here" -name "*.cuh" -newer "$obj")" || "$here/../include/arbius_b200.h" -nt "$obj" ]]; then
     "$NVCC" "${FLAGS[@]}" -Xptxas -v -c "$src" -o "$obj" 2> "$obj.log" &
     pids+=($!)
   fi
