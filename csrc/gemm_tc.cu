@@ -62,6 +62,11 @@ struct GemmParams {
     int tma_store;
     int mt;                     // 128-row M tiles per CTA (1 or 2)
     int deep;                   // one CTA per SM at most: use the deep-pipeline instantiation (see launch_gemm)
+    // Split-K inside a thread-block cluster: the `splitk` CTAs of one output tile form a cluster along grid z; every CTA
+    // but the first parks its fp32 accumulator in its own shared memory, the first adds them to its own in split order
+    // through distributed shared memory and runs the real epilogue. Same partial sums, same order, same bytes as the
+    // workspace + splitk_reduce_kernel path, without the fp32 round trip through HBM and without the second launch.
+    int cluster_k;
     // cross-GPU hand-off folded into the kernel (patch parallelism): the producer thread waits for the ranks in
     // sync_wait_mask to publish *sync_tick in this GPU's copy of the site before its first load (halo rows arrived)
     const unsigned int* sync_tick;
@@ -169,6 +174,20 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
     }
 }
 
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;\n" ::: "memory");
+}
+__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_smem_addr, uint32_t cta_rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(local_smem_addr), "r"(cta_rank));
+    return r;
+}
+__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];\n" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
 // MT = 2: one CTA owns two M-adjacent 128-row tiles (two accumulators in TMEM) that share every weight tile it
 // loads. Shared-memory ingest per MMA cycle drops from (A + B) / t to (2A + B) / 2t: the 128 x 256 tile needs
 // ~94 B/clk at tensor peak against the ~64 B/clk an SM can take from L2 (680 cycles per K step measured, 512 ideal),
@@ -186,6 +205,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "UMMA N for M=128; epilogue reads 32-column chunks");
     static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment");
     static_assert(MT * (BN / 32) * BM * 64 <= STAGES * STAGE_BYTES, "output staging boxes reuse the pipeline stages");
+    static_assert(BM * BN * 4 <= STAGES * STAGE_BYTES, "a parked fp32 accumulator reuses the pipeline stages");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -327,14 +347,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             umma_commit(acc_bar);                 // accumulator complete
             if (dbg) dbg[2] = clock64() - t_start;                     // all MMAs issued
         }
-    } else {
-        // ================= epilogue warps =================
+    }
+    // ================= epilogue warps =================
+    // mode 0: the whole epilogue (no cluster). mode 1: cluster split-K, not the first split: park the fp32 accumulator
+    // in this CTA's (drained) pipeline buffers as [chunk][row][32 floats]. mode 2: first split of a cluster: add the
+    // other splits' accumulators in split order through DSMEM, then the real epilogue.
+    auto epilogue = [&](const int mode) {
         const int q = warp & 3;                   // TMEM lane quarter this warp may read
         const int hf = (warp - 2) >> 2;           // which half of the 32-column chunks this warp handles
         const int r = q * 32 + lane;              // row inside the tile
         // While the main loop runs, stage bias (+ row bias if a whole sub-tile shares one group) in smem.
         bool single_group[MT];
-        const bool use_sb = p.splitk <= 1;
+        const bool use_sb = p.splitk <= 1 || mode == 2;
+        float* const part = reinterpret_cast<float*>(smem);
 #pragma unroll
         for (int s = 0; s < MT; ++s) {
             int tile_grp;
@@ -401,6 +426,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tmem_wait_ld();
             if (PF && j + 1 < MY_MAX && c + 2 < NCHUNK) tmem_ld32(taddr + (c + 2) * 32, raw[PF ? ((j + 1) & 1) : 0]);
             const int n_base = n0 + c * 32;
+            if (mode == 1) {
+                float4* dst = reinterpret_cast<float4*>(part + (static_cast<size_t>(c) * BM + r) * 32);
+#pragma unroll
+                for (int g = 0; g < 8; ++g)
+                    dst[g] = make_float4(__uint_as_float(raw[PF ? (j & 1) : 0][4 * g]), __uint_as_float(raw[PF ? (j & 1) : 0][4 * g + 1]),
+                                         __uint_as_float(raw[PF ? (j & 1) : 0][4 * g + 2]), __uint_as_float(raw[PF ? (j & 1) : 0][4 * g + 3]));
+                continue;
+            }
+            // (0 + p0) + p1 + ...: the workspace path starts from zero, and 0 + (-0) is +0
+            auto add_splits = [&](float (&v)[32]) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __fadd_rn(0.f, v[i]);
+                const uint32_t mine = smem_u32(part + (static_cast<size_t>(c) * BM + r) * 32);
+                for (int z = 1; z < p.cluster_k; ++z) {
+                    const uint32_t ra = dsmem_addr(mine, static_cast<uint32_t>(z));
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) {
+                        const float4 t = ld_dsmem_f4(ra + 16 * g);
+                        v[4 * g] += t.x; v[4 * g + 1] += t.y; v[4 * g + 2] += t.z; v[4 * g + 3] += t.w;
+                    }
+                }
+            };
             if (p.tma_store) {
                 if (n_base >= p.N) continue;                           // warp-uniform: the whole box is out of range
                 uint8_t* box = stage_base + c * (BM * 64);
@@ -408,6 +455,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     float v[32];
 #pragma unroll
                     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
+                    if (mode == 2) add_splits(v);
                     epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias_s + c * 32, rowbias_global, box + r * 64,
                                              (r >> 1) & 3);
                 }
@@ -424,7 +472,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 float v[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
-                if (p.splitk > 1) {
+                if (mode == 2) add_splits(v);
+                if (p.splitk > 1 && mode == 0) {
                     const int owner = static_cast<int>(out_row / p.rows_per_owner);
                     float* ws = p.ws_peer[owner] + (static_cast<long long>(p.z_base + blockIdx.z) * p.rows_per_owner +
                                                     (out_row - static_cast<long long>(owner) * p.rows_per_owner)) * p.N + n_base;
@@ -438,7 +487,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
         }   // sub-tiles
-        if (p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
+        if (mode != 1 && p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
+    };
+    const bool ck = p.cluster_k > 1;
+    if (warp >= 2 && !(ck && blockIdx.z == 0)) epilogue(ck ? 1 : 0);
+    if (ck) {
+        cluster_sync_all();                       // every split's accumulator is parked (or, for the first, in its TMEM)
+        if (warp >= 2 && blockIdx.z == 0) epilogue(2);
+        cluster_sync_all();                       // the first split has read them: the others may exit
     }
 
     if (dbg && threadIdx.x == 64) dbg[4] = clock64() - t_start;       // epilogue done
@@ -572,7 +628,23 @@ static int launch_gemm_mt(const CUtensorMap& tmA, const CUtensorMap& tmA2, const
     constexpr int smem = STAGES * (MT * BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 32 + MT * BN * 4 + 1024;
     static_assert(smem <= 227 * 1024, "stage count does not fit shared memory");
     if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, STAGES, T, EPI, MT>), smem)) return -1;
-    AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI, MT>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
+    if (p.cluster_k > 1) {
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(GEMM_THREADS);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 1;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = static_cast<unsigned>(p.cluster_k);
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES, T, EPI, MT>, tmA, tmA2, tmB, p));
+    } else {
+        AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI, MT>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
+    }
     ab_count_launch(1);
     return 0;
 }
@@ -638,6 +710,18 @@ extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, c
 #else
 extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, const CUtensorMap* tmA2, const CUtensorMap* tmB,
                                  const void* params, unsigned gx, unsigned gy, unsigned gz, void* stream);
+
+// Split-K through a thread-block cluster (default) or through the fp32 workspace + reduce kernel (AB_SPLITK_CLUSTER=0,
+// or ab_gemm_set_cluster_splitk(0) at run time: the tests compare the two paths bit for bit).
+static int g_cluster_splitk = -1;
+extern "C" int ab_gemm_cluster_splitk_enabled(void) {
+    if (g_cluster_splitk < 0) {
+        const char* e = getenv("AB_SPLITK_CLUSTER");
+        g_cluster_splitk = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_cluster_splitk;
+}
+extern "C" void ab_gemm_set_cluster_splitk(int on) { g_cluster_splitk = on ? 1 : 0; }
 
 static long long* g_gemm_dbg = nullptr;
 // Profiling aid: point at a device buffer of >= 8 * grid_size int64 to receive per-CTA phase cycle counts.
@@ -724,7 +808,8 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         }
         p.workspace = p.ws_peer[d->rs_rank];
     }
-    if (splitk > 1) AB_REQUIRE(p.workspace, "split-K needs a workspace");
+    p.cluster_k = (ab_gemm_cluster_splitk_enabled() && splitk > 1 && splitk <= 8 && !rs) ? splitk : 0;
+    if (splitk > 1 && !p.cluster_k) AB_REQUIRE(p.workspace, "split-K needs a workspace");
     if (ag) {
         AB_REQUIRE(!a->conv && a->K2 == 0, "all-gather mode: linear GEMM without virtual concat");
         AB_REQUIRE(d->nsrc == 2 || d->nsrc == 4 || d->nsrc == 8, "all-gather mode: 2/4/8 sources");
@@ -779,7 +864,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
 
     static const bool tma_store_on = [] { const char* e = getenv("AB_TMA_STORE"); return !(e && e[0] == '0'); }();
     p.tma_store = 0;
-    if (tma_store_on && !a->geglu && splitk <= 1 && !rs && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0) {
+    if (tma_store_on && !a->geglu && (splitk <= 1 || p.cluster_k) && !rs && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0) {
         const uint64_t ld = (uint64_t)p.ldo * esz;
         if (a->conv) {
             uint64_t dims[4] = {(uint64_t)a->N, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
@@ -799,7 +884,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     const int n_tiles = (a->N + bn - 1) / bn;
     // two tiles per CTA: only for long main loops (the doubled epilogue is serial behind them: 512x512x128->128 with
     // 18 K steps got 20 % slower) on problems that still give every SM two waves
-    p.mt = (mt_on && !ag && bn == 256 && tiles_m % 2 == 0 && p.chunks_per_split >= 24 &&
+    p.mt = (mt_on && !ag && !p.cluster_k && bn == 256 && tiles_m % 2 == 0 && p.chunks_per_split >= 24 &&
             static_cast<long long>(tiles_m / 2) * n_tiles * grid_z >= 2LL * ab_sm_count()) ? 2 : 1;
     dim3 grid(tiles_m / p.mt, n_tiles, grid_z);
     static const bool deep_on = [] { const char* e = getenv("AB_GEMM_DEEP"); return !(e && e[0] == '0'); }();
@@ -810,14 +895,14 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
             : a->act == ACT_SILU ? EPI_SILU
             : a->act == ACT_GELU ? EPI_GELU
             : a->act == ACT_QUICK_GELU ? EPI_QGELU : EPI_ANY;
-    const int main_epi = splitk > 1 ? EPI_NONE : epi;     // with split-K the main kernel only stores fp32 partials
+    const int main_epi = (splitk > 1 && !p.cluster_k) ? EPI_NONE : epi;   // workspace split-K: the main kernel only stores fp32 partials
     int rc = 0;
     if (phase != 2) {
         if (a->dtype == AB_BF16) rc = ab_gemm_main_bf16(main_epi, bn, &tmA, &tmA2, &tmB, &p, grid.x, grid.y, grid.z, stream_);
         else rc = gemm_main_t<__half>(main_epi, bn, tmA, tmA2, tmB, p, grid, stream);
     }
     if (rc) return rc;
-    if (splitk > 1 && phase != 1) {
+    if (splitk > 1 && phase != 1 && !p.cluster_k) {
         if (rs) { p.M = p.rows_per_owner; p.splitk = 8; }      // owners reduce their own row band
         // one thread per (row, 32-column chunk); 64-thread blocks keep many CTAs in flight for small M*N
         const long long work = static_cast<long long>(p.M) * ((p.N + 31) / 32);

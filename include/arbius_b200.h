@@ -93,6 +93,11 @@ typedef struct {
 } ab_gemm_dist_args;
 int ab_gemm_dist(const ab_gemm_args* args, const ab_gemm_dist_args* dist, int phase, void* stream);
 size_t ab_gemm_workspace_bytes(const ab_gemm_args* args);
+/* splitk > 1 runs by default as ONE launch: the splitk CTAs of an output tile form a thread-block cluster, park their
+ * fp32 accumulators in shared memory and the first CTA adds them in split order through distributed shared memory
+ * before the epilogue. Bit-identical to the workspace + second-kernel path (0 selects that path; env AB_SPLITK_CLUSTER). */
+int ab_gemm_cluster_splitk_enabled(void);
+void ab_gemm_set_cluster_splitk(int on);
 
 /* ---- K1 small-channel direct conv (conv_in / conv_out, Cin or Cout < 64) ------------------------ */
 /* x [N,H,W,Cin] -> out [N,Ho,Wo,Cout], pad = KH/2, stride 1 or 2. Weight layout by shape class:
