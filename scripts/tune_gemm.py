@@ -99,9 +99,18 @@ def bench_key(key, dt=torch.float16, only_splitk=None):
     return res, flops, wbytes
 
 
+def _load_table():
+    """The table being built in this gpurun call (gpurun_out/) if there is one, else the tree's."""
+    import os
+    for path in ("gpurun_out/tuned_sm100.json", "arbius_b200/ops/tuned_sm100.json"):
+        if os.path.exists(path):
+            return json.load(open(path))
+    return {}
+
+
 def tune_batched(a):
     """For every tuned canonical shape: the same op with task_batch x the rows, split-K fixed, best block_n."""
-    canon = json.load(open("arbius_b200/ops/tuned_sm100.json"))
+    canon = _load_table()
     out = {}
     for key, (bn0, sk) in sorted(canon.items()):
         parts = key.split(":")
@@ -114,8 +123,6 @@ def tune_batched(a):
             big = f"{parts[0]}:{int(parts[1]) * a.task_batch}:{parts[2]}:{parts[3]}"
         else:
             continue
-        if big in canon:
-            continue
         res, flops, _ = bench_key(big, only_splitk=sk)
         (bn, _), us = min(res.items(), key=lambda kv: kv[1])
         base = res.get((bn0, sk), float("nan"))
@@ -123,6 +130,8 @@ def tune_batched(a):
         print(json.dumps(dict(key=big, canonical=[bn0, sk], best_bn=bn, us=round(us, 2), canonical_bn_us=round(base, 2),
                               tflops=round(flops / us / 1e6, 1))), flush=True)
     json.dump(out, open(a.out.replace(".json", f"_tb{a.task_batch}.json"), "w"), indent=0, sort_keys=True)
+    canon.update(out)
+    json.dump(canon, open("gpurun_out/tuned_sm100.json", "w"), indent=0, sort_keys=True)
 
 
 def tune_kandinsky(a):
@@ -140,7 +149,7 @@ def tune_kandinsky(a):
     G.RECORD = None
     del pipe
     torch.cuda.empty_cache()
-    table = json.load(open("arbius_b200/ops/tuned_sm100.json"))
+    table = _load_table()
     new, report = {}, []
     for key, cnt in sorted(counts.items(), key=lambda kv: -kv[1]):
         parts = key.split(":")
@@ -149,7 +158,7 @@ def tune_kandinsky(a):
             m = b_ * h * w
         else:
             m = int(parts[1])
-        if m < 256 or key in table:
+        if m < 256 or (key in table and not a.retune):
             continue                                   # tiny per-task GEMMs (embeddings, prior): the heuristic is fine
         res, flops, _ = bench_key(key)
         (bn, sk), us = min(res.items(), key=lambda kv: kv[1])
@@ -166,7 +175,7 @@ def tune_kandinsky(a):
                 if m % (P * 8):
                     continue
                 band = f"{parts[0]}:{m // P}:{parts[2]}:{parts[3]}"
-            if band in table or band in new:
+            if band in new or (band in table and not a.retune):
                 continue
             r2, f2, _ = bench_key(band, only_splitk=sk)
             (bn2, _), us2 = min(r2.items(), key=lambda kv: kv[1])
@@ -183,6 +192,7 @@ def tune_kandinsky(a):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "kandinsky2"])
+    ap.add_argument("--retune", action="store_true", help="measure shapes again even if the table has them")
     ap.add_argument("--bands", type=lambda v: [int(x) for x in v.split(",")], default=[2, 4, 8])
     ap.add_argument("--write", action="store_true")
     ap.add_argument("--out", default="gpurun_out/tune_report.json")
@@ -224,7 +234,9 @@ def main():
         print(json.dumps({k: v for k, v in report[-1].items() if k != "all"}), flush=True)
     json.dump(report, open(a.out, "w"), indent=1)
     if a.write:
-        json.dump(table, open("gpurun_out/tuned_sm100.json", "w"), indent=0, sort_keys=True)
+        merged = _load_table()
+        merged.update(table)
+        json.dump(merged, open("gpurun_out/tuned_sm100.json", "w"), indent=0, sort_keys=True)
 
 
 if __name__ == "__main__":

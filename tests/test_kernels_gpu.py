@@ -312,6 +312,8 @@ def test_cluster_splitk_equals_workspace_splitk_bit_for_bit(splitk):
     """Split-K through a thread-block cluster (accumulators parked in shared memory, summed by the first CTA through
     DSMEM) must give the bytes of the fp32-workspace + reduce-kernel path: same partial sums, same order."""
     import ctypes as C
+
+    from arbius_b200 import ops
     lib = ops.native.load()
     lib.ab_gemm_set_cluster_splitk.argtypes = [C.c_int]
     torch.manual_seed(splitk)
