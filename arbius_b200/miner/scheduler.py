@@ -230,6 +230,7 @@ def simulate(tasks: Sequence[Tuple[float, str]], n_gpus: int, cost: CostModel, p
     pending: List[Tuple[float, int, str]] = []
     running: List[Tuple[float, Tuple[int, ...]]] = []
     lat: List[float] = []
+    assignments: List[List[int]] = []
     now, i, seq = 0.0, 0, 0
     arrivals = sorted(tasks)
     while i < len(arrivals) or pending or running:
@@ -251,6 +252,7 @@ def simulate(tasks: Sequence[Tuple[float, str]], n_gpus: int, cost: CostModel, p
                     end = now + cost.ms(fam, p) / 1e3
                     heapq.heappush(running, (end, gpus))
                     lat.append(end - arr)
+                    assignments.append(list(gpus))
                     progressed = True
         # advance time
         nxt = []
@@ -266,4 +268,4 @@ def simulate(tasks: Sequence[Tuple[float, str]], n_gpus: int, cost: CostModel, p
             planner.release(gpus)
     lat.sort()
     return {"tasks_per_hour": len(lat) / max(now, 1e-9) * 3600.0, "p50_latency_s": lat[len(lat) // 2] if lat else 0.0,
-            "makespan_s": now}
+            "makespan_s": now, "assignments": assignments}
