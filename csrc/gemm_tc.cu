@@ -205,7 +205,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "UMMA N for M=128; epilogue reads 32-column chunks");
     static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment");
     static_assert(MT * (BN / 32) * BM * 64 <= STAGES * STAGE_BYTES, "output staging boxes reuse the pipeline stages");
-    static_assert(BM * BN * 4 <= STAGES * STAGE_BYTES, "a parked fp32 accumulator reuses the pipeline stages");
+    // cluster split-K (>= 2 CTAs): the parked fp32 accumulator and the boxes of the chunks this CTA owns share the stages
+    static_assert(BM * BN * 4 + ((BN / 32 + 1) / 2) * BM * 64 <= STAGES * STAGE_BYTES, "parked accumulator + owned output boxes");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -349,17 +350,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
     }
     // ================= epilogue warps =================
-    // mode 0: the whole epilogue (no cluster). mode 1: cluster split-K, not the first split: park the fp32 accumulator
-    // in this CTA's (drained) pipeline buffers as [chunk][row][32 floats]. mode 2: first split of a cluster: add the
-    // other splits' accumulators in split order through DSMEM, then the real epilogue.
-    auto epilogue = [&](const int mode) {
+    // Without a cluster: tcgen05.ld the accumulator chunk by chunk and run the epilogue. Cluster split-K (cluster_k > 1):
+    // every CTA of the cluster first parks its fp32 accumulator in its own (drained) pipeline buffers as
+    // [chunk][row][32 floats]; after a cluster barrier CTA z owns the 32-column chunks c = z, z + S, ... of the tile,
+    // adds the S parked accumulators of each in split order through distributed shared memory and runs the epilogue
+    // for them — the reduction and the epilogue are spread over all S CTAs instead of queueing behind one.
+    const bool ck = p.cluster_k > 1;
+    float* const part = reinterpret_cast<float*>(smem);
+    if (ck && warp >= 2) {
+        const int q = warp & 3, hf = (warp - 2) >> 2, r = q * 32 + lane;
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        for (int c = hf; c < BN / 32; c += 2) {
+            uint32_t raw[32];
+            tmem_ld32(taddr + c * 32, raw);
+            tmem_wait_ld();
+            float4* dst = reinterpret_cast<float4*>(part + (static_cast<size_t>(c) * BM + r) * 32);
+#pragma unroll
+            for (int g = 0; g < 8; ++g)
+                dst[g] = make_float4(__uint_as_float(raw[4 * g]), __uint_as_float(raw[4 * g + 1]),
+                                     __uint_as_float(raw[4 * g + 2]), __uint_as_float(raw[4 * g + 3]));
+        }
+    }
+    if (ck) cluster_sync_all();                   // every split's accumulator is parked
+    if (warp >= 2) {
         const int q = warp & 3;                   // TMEM lane quarter this warp may read
         const int hf = (warp - 2) >> 2;           // which half of the 32-column chunks this warp handles
         const int r = q * 32 + lane;              // row inside the tile
         // While the main loop runs, stage bias (+ row bias if a whole sub-tile shares one group) in smem.
         bool single_group[MT];
-        const bool use_sb = p.splitk <= 1 || mode == 2;
-        float* const part = reinterpret_cast<float*>(smem);
+        const bool use_sb = p.splitk <= 1 || ck;
 #pragma unroll
         for (int s = 0; s < MT; ++s) {
             int tile_grp;
@@ -384,15 +405,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
         if (use_sb) asm volatile("bar.sync 1, 256;\n" ::: "memory");
-        mbar_wait(acc_bar, 0);
-        tc_fence_after();
+        if (!ck) {
+            mbar_wait(acc_bar, 0);
+            tc_fence_after();
+        }
         if (dbg && threadIdx.x == 64) dbg[3] = clock64() - t_start;   // accumulator ready
 #pragma unroll
         for (int s = 0; s < MT; ++s) {
         const int w0 = w0s[s], h0 = h0s[s], i0 = i0s[s], m0 = m0s[s];
         const bool rowbias_global = !single_group[s];
         float* const sbias_s = sbias + s * BN;
-        uint8_t* const stage_base = smem + s * ((BN / 32) * BM * 64);
+        // output boxes are staged behind the parked accumulator when there is one (the peers are still reading it)
+        uint8_t* const stage_base = smem + (ck ? BM * BN * 4 : 0) + s * ((BN / 32) * BM * 64);
         long long out_row;
         int grp;
         bool row_ok;
@@ -417,48 +441,44 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // (the prefetch needs a second 32-register buffer: only where one CTA per SM leaves the registers free)
         constexpr bool PF = BN > 160;
         uint32_t raw[PF ? 2 : 1][32];
-        if (PF && hf < NCHUNK) tmem_ld32(taddr + hf * 32, raw[0]);
+        if (!ck && PF && hf < NCHUNK) tmem_ld32(taddr + hf * 32, raw[0]);
+        const int S = ck ? p.cluster_k : 1;
+        const int z = ck ? static_cast<int>(blockIdx.z) : 0;
 #pragma unroll
         for (int j = 0; j < MY_MAX; ++j) {
-            const int c = 2 * j + hf;
+            // without a cluster: chunk 2j + hf. In a cluster: the (2j + hf)-th chunk this CTA owns.
+            const int c = ck ? z + (2 * j + hf) * S : 2 * j + hf;
             if (c >= NCHUNK) break;
-            if (!PF) tmem_ld32(taddr + c * 32, raw[0]);
-            tmem_wait_ld();
-            if (PF && j + 1 < MY_MAX && c + 2 < NCHUNK) tmem_ld32(taddr + (c + 2) * 32, raw[PF ? ((j + 1) & 1) : 0]);
-            const int n_base = n0 + c * 32;
-            if (mode == 1) {
-                float4* dst = reinterpret_cast<float4*>(part + (static_cast<size_t>(c) * BM + r) * 32);
+            float v[32];
+            if (ck) {
+                // (0 + p0) + p1 + ...: the workspace path starts from zero, and 0 + (-0) is +0
 #pragma unroll
-                for (int g = 0; g < 8; ++g)
-                    dst[g] = make_float4(__uint_as_float(raw[PF ? (j & 1) : 0][4 * g]), __uint_as_float(raw[PF ? (j & 1) : 0][4 * g + 1]),
-                                         __uint_as_float(raw[PF ? (j & 1) : 0][4 * g + 2]), __uint_as_float(raw[PF ? (j & 1) : 0][4 * g + 3]));
-                continue;
-            }
-            // (0 + p0) + p1 + ...: the workspace path starts from zero, and 0 + (-0) is +0
-            auto add_splits = [&](float (&v)[32]) {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __fadd_rn(0.f, v[i]);
+                for (int i = 0; i < 32; ++i) v[i] = 0.f;
                 const uint32_t mine = smem_u32(part + (static_cast<size_t>(c) * BM + r) * 32);
-                for (int z = 1; z < p.cluster_k; ++z) {
-                    const uint32_t ra = dsmem_addr(mine, static_cast<uint32_t>(z));
+                for (int zz = 0; zz < S; ++zz) {
+                    const uint32_t ra = dsmem_addr(mine, static_cast<uint32_t>(zz));
+                    float4 t[8];
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) t[g] = ld_dsmem_f4(ra + 16 * g);
 #pragma unroll
                     for (int g = 0; g < 8; ++g) {
-                        const float4 t = ld_dsmem_f4(ra + 16 * g);
-                        v[4 * g] += t.x; v[4 * g + 1] += t.y; v[4 * g + 2] += t.z; v[4 * g + 3] += t.w;
+                        v[4 * g] += t[g].x; v[4 * g + 1] += t[g].y; v[4 * g + 2] += t[g].z; v[4 * g + 3] += t[g].w;
                     }
                 }
-            };
+            } else {
+                if (!PF) tmem_ld32(taddr + c * 32, raw[0]);
+                tmem_wait_ld();
+                if (PF && j + 1 < MY_MAX && c + 2 < NCHUNK) tmem_ld32(taddr + (c + 2) * 32, raw[PF ? ((j + 1) & 1) : 0]);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
+            }
+            const int n_base = n0 + c * 32;
             if (p.tma_store) {
                 if (n_base >= p.N) continue;                           // warp-uniform: the whole box is out of range
-                uint8_t* box = stage_base + c * (BM * 64);
-                if (row_ok) {
-                    float v[32];
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
-                    if (mode == 2) add_splits(v);
+                uint8_t* box = stage_base + (ck ? 2 * j + hf : c) * (BM * 64);    // cluster: one box per OWNED chunk
+                if (row_ok)
                     epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias_s + c * 32, rowbias_global, box + r * 64,
                                              (r >> 1) & 3);
-                }
                 fence_proxy_async();
                 asm volatile("bar.sync %0, 128;\n" ::"r"(2 + hf) : "memory");   // the four warps of this chunk parity
                 if (q == 0 && lane == 0) {
@@ -469,11 +489,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 continue;
             }
             if (row_ok && n_base < p.N) {
-                float v[32];
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
-                if (mode == 2) add_splits(v);
-                if (p.splitk > 1 && mode == 0) {
+                if (p.splitk > 1 && !ck) {
                     const int owner = static_cast<int>(out_row / p.rows_per_owner);
                     float* ws = p.ws_peer[owner] + (static_cast<long long>(p.z_base + blockIdx.z) * p.rows_per_owner +
                                                     (out_row - static_cast<long long>(owner) * p.rows_per_owner)) * p.N + n_base;
@@ -487,15 +503,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
         }   // sub-tiles
-        if (mode != 1 && p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
-    };
-    const bool ck = p.cluster_k > 1;
-    if (warp >= 2 && !(ck && blockIdx.z == 0)) epilogue(ck ? 1 : 0);
-    if (ck) {
-        cluster_sync_all();                       // every split's accumulator is parked (or, for the first, in its TMEM)
-        if (warp >= 2 && blockIdx.z == 0) epilogue(2);
-        cluster_sync_all();                       // the first split has read them: the others may exit
+        if (p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
     }
+    if (ck) cluster_sync_all();                   // every CTA has read the parked accumulators: all may exit
 
     if (dbg && threadIdx.x == 64) dbg[4] = clock64() - t_start;       // epilogue done
     // ---- teardown -----------------------------------------------------------------------------

@@ -210,7 +210,7 @@ def main():
     G.RECORD = []
     pipe.generate("cat", "", a.size, a.size, 2, 7.5, "DPMSolverMultistep", seed=1)
     torch.cuda.synchronize()
-    counts = Counter(G.RECORD)
+    counts = Counter(k for k in G.RECORD if k.split(":")[0] in ("lin", "geglu", "conv"))
     G.RECORD = None
     del pipe
     torch.cuda.empty_cache()
