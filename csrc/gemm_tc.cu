@@ -366,10 +366,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             uint32_t raw[32];
             tmem_ld32(taddr + c * 32, raw);
             tmem_wait_ld();
+            // 16-byte slot g of row r sits at slot g ^ (r & 7): the eight lanes of a quarter-warp, whose rows are 128
+            // bytes apart, then hit eight different bank groups instead of one (an 8-way conflict per access, measured
+            // as ~3 us per parked accumulator in the first cut)
             float4* dst = reinterpret_cast<float4*>(part + (static_cast<size_t>(c) * BM + r) * 32);
 #pragma unroll
             for (int g = 0; g < 8; ++g)
-                dst[g] = make_float4(__uint_as_float(raw[4 * g]), __uint_as_float(raw[4 * g + 1]),
+                dst[g ^ (r & 7)] = make_float4(__uint_as_float(raw[4 * g]), __uint_as_float(raw[4 * g + 1]),
                                      __uint_as_float(raw[4 * g + 2]), __uint_as_float(raw[4 * g + 3]));
         }
     }
@@ -459,7 +462,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const uint32_t ra = dsmem_addr(mine, static_cast<uint32_t>(zz));
                     float4 t[8];
 #pragma unroll
-                    for (int g = 0; g < 8; ++g) t[g] = ld_dsmem_f4(ra + 16 * g);
+                    for (int g = 0; g < 8; ++g) t[g] = ld_dsmem_f4(ra + 16 * (g ^ (r & 7)));
 #pragma unroll
                     for (int g = 0; g < 8; ++g) {
                         v[4 * g] += t[g].x; v[4 * g + 1] += t[g].y; v[4 * g + 2] += t[g].z; v[4 * g + 3] += t[g].w;
@@ -721,13 +724,17 @@ extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, c
 extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, const CUtensorMap* tmA2, const CUtensorMap* tmB,
                                  const void* params, unsigned gx, unsigned gy, unsigned gz, void* stream);
 
-// Split-K through a thread-block cluster (default) or through the fp32 workspace + reduce kernel (AB_SPLITK_CLUSTER=0,
-// or ab_gemm_set_cluster_splitk(0) at run time: the tests compare the two paths bit for bit).
+// Split-K through the fp32 workspace + reduce kernel (default) or inside a thread-block cluster (AB_SPLITK_CLUSTER=1, or
+// ab_gemm_set_cluster_splitk(1) at run time: the tests compare the two paths bit for bit). Measured on B200
+// (scripts/phase_splitk.py, 48x48x768 conv, BN 256): the cluster form saves the second launch and the HBM round trip
+// but its DSMEM reads cost ~4 us per split and its two cluster barriers hold every SM of the cluster until the slowest
+// CTA is through — 78 vs 76 us at two splits, 131 vs 87 at four, 173 vs 114 at six. It stays opt-in until the
+// cross-SM reads are restructured (more loads in flight per thread).
 static int g_cluster_splitk = -1;
 extern "C" int ab_gemm_cluster_splitk_enabled(void) {
     if (g_cluster_splitk < 0) {
         const char* e = getenv("AB_SPLITK_CLUSTER");
-        g_cluster_splitk = (e && e[0] == '0') ? 0 : 1;
+        g_cluster_splitk = (e && e[0] == '1') ? 1 : 0;
     }
     return g_cluster_splitk;
 }

@@ -93,9 +93,10 @@ typedef struct {
 } ab_gemm_dist_args;
 int ab_gemm_dist(const ab_gemm_args* args, const ab_gemm_dist_args* dist, int phase, void* stream);
 size_t ab_gemm_workspace_bytes(const ab_gemm_args* args);
-/* splitk > 1 runs by default as ONE launch: the splitk CTAs of an output tile form a thread-block cluster, park their
- * fp32 accumulators in shared memory and the first CTA adds them in split order through distributed shared memory
- * before the epilogue. Bit-identical to the workspace + second-kernel path (0 selects that path; env AB_SPLITK_CLUSTER). */
+/* splitk > 1 can run as ONE launch (opt-in: 1 here or env AB_SPLITK_CLUSTER=1): the splitk CTAs of an output tile form
+ * a thread-block cluster, park their fp32 accumulators in shared memory, and every CTA adds the parked accumulators of
+ * the 32-column chunks it owns in split order through distributed shared memory before the epilogue. Bit-identical to
+ * the default workspace + second-kernel path, which measured faster on B200 beyond two splits (see csrc/gemm_tc.cu). */
 int ab_gemm_cluster_splitk_enabled(void);
 void ab_gemm_set_cluster_splitk(int on);
 

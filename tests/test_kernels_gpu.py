@@ -339,4 +339,4 @@ def test_cluster_splitk_equals_workspace_splitk_bit_for_bit(splitk):
                 got = fn(bn)
                 assert torch.equal(got, want), f"splitk={splitk} bn={bn}"
     finally:
-        lib.ab_gemm_set_cluster_splitk(1)
+        lib.ab_gemm_set_cluster_splitk(0)              # the library default
