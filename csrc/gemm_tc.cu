@@ -61,12 +61,6 @@ struct GemmParams {
     // scattered over 32 rows per warp instruction. Off for GEGLU, split-K partials and reduce-scatter.
     int tma_store;
     int mt;                     // 128-row M tiles per CTA (1 or 2)
-    int deep;                   // one CTA per SM at most: use the deep-pipeline instantiation (see launch_gemm)
-    // Split-K inside a thread-block cluster: the `splitk` CTAs of one output tile form a cluster along grid z; every CTA
-    // but the first parks its fp32 accumulator in its own shared memory, the first adds them to its own in split order
-    // through distributed shared memory and runs the real epilogue. Same partial sums, same order, same bytes as the
-    // workspace + splitk_reduce_kernel path, without the fp32 round trip through HBM and without the second launch.
-    int cluster_k;
     // cross-GPU hand-off folded into the kernel (patch parallelism): the producer thread waits for the ranks in
     // sync_wait_mask to publish *sync_tick in this GPU's copy of the site before its first load (halo rows arrived)
     const unsigned int* sync_tick;
@@ -174,20 +168,6 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
     }
 }
 
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;\n" ::: "memory");
-}
-__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_smem_addr, uint32_t cta_rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(local_smem_addr), "r"(cta_rank));
-    return r;
-}
-__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t addr) {
-    float4 v;
-    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];\n" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
-    return v;
-}
-
 // MT = 2: one CTA owns two M-adjacent 128-row tiles (two accumulators in TMEM) that share every weight tile it
 // loads. Shared-memory ingest per MMA cycle drops from (A + B) / t to (2A + B) / 2t: the 128 x 256 tile needs
 // ~94 B/clk at tensor peak against the ~64 B/clk an SM can take from L2 (680 cycles per K step measured, 512 ideal),
@@ -205,8 +185,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "UMMA N for M=128; epilogue reads 32-column chunks");
     static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment");
     static_assert(MT * (BN / 32) * BM * 64 <= STAGES * STAGE_BYTES, "output staging boxes reuse the pipeline stages");
-    // cluster split-K (>= 2 CTAs): the parked fp32 accumulator and the boxes of the chunks this CTA owns share the stages
-    static_assert(BM * BN * 4 + ((BN / 32 + 1) / 2) * BM * 64 <= STAGES * STAGE_BYTES, "parked accumulator + owned output boxes");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -348,42 +326,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             umma_commit(acc_bar);                 // accumulator complete
             if (dbg) dbg[2] = clock64() - t_start;                     // all MMAs issued
         }
-    }
-    // ================= epilogue warps =================
-    // Without a cluster: tcgen05.ld the accumulator chunk by chunk and run the epilogue. Cluster split-K (cluster_k > 1):
-    // every CTA of the cluster first parks its fp32 accumulator in its own (drained) pipeline buffers as
-    // [chunk][row][32 floats]; after a cluster barrier CTA z owns the 32-column chunks c = z, z + S, ... of the tile,
-    // adds the S parked accumulators of each in split order through distributed shared memory and runs the epilogue
-    // for them — the reduction and the epilogue are spread over all S CTAs instead of queueing behind one.
-    const bool ck = p.cluster_k > 1;
-    float* const part = reinterpret_cast<float*>(smem);
-    if (ck && warp >= 2) {
-        const int q = warp & 3, hf = (warp - 2) >> 2, r = q * 32 + lane;
-        mbar_wait(acc_bar, 0);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-        for (int c = hf; c < BN / 32; c += 2) {
-            uint32_t raw[32];
-            tmem_ld32(taddr + c * 32, raw);
-            tmem_wait_ld();
-            // 16-byte slot g of row r sits at slot g ^ (r & 7): the eight lanes of a quarter-warp, whose rows are 128
-            // bytes apart, then hit eight different bank groups instead of one (an 8-way conflict per access, measured
-            // as ~3 us per parked accumulator in the first cut)
-            float4* dst = reinterpret_cast<float4*>(part + (static_cast<size_t>(c) * BM + r) * 32);
-#pragma unroll
-            for (int g = 0; g < 8; ++g)
-                dst[g ^ (r & 7)] = make_float4(__uint_as_float(raw[4 * g]), __uint_as_float(raw[4 * g + 1]),
-                                     __uint_as_float(raw[4 * g + 2]), __uint_as_float(raw[4 * g + 3]));
-        }
-    }
-    if (ck) cluster_sync_all();                   // every split's accumulator is parked
-    if (warp >= 2) {
+    } else {
+        // ================= epilogue warps =================
         const int q = warp & 3;                   // TMEM lane quarter this warp may read
         const int hf = (warp - 2) >> 2;           // which half of the 32-column chunks this warp handles
         const int r = q * 32 + lane;              // row inside the tile
         // While the main loop runs, stage bias (+ row bias if a whole sub-tile shares one group) in smem.
         bool single_group[MT];
-        const bool use_sb = p.splitk <= 1 || ck;
+        const bool use_sb = p.splitk <= 1;
 #pragma unroll
         for (int s = 0; s < MT; ++s) {
             int tile_grp;
@@ -408,18 +358,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
         if (use_sb) asm volatile("bar.sync 1, 256;\n" ::: "memory");
-        if (!ck) {
-            mbar_wait(acc_bar, 0);
-            tc_fence_after();
-        }
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
         if (dbg && threadIdx.x == 64) dbg[3] = clock64() - t_start;   // accumulator ready
 #pragma unroll
         for (int s = 0; s < MT; ++s) {
         const int w0 = w0s[s], h0 = h0s[s], i0 = i0s[s], m0 = m0s[s];
         const bool rowbias_global = !single_group[s];
         float* const sbias_s = sbias + s * BN;
-        // output boxes are staged behind the parked accumulator when there is one (the peers are still reading it)
-        uint8_t* const stage_base = smem + (ck ? BM * BN * 4 : 0) + s * ((BN / 32) * BM * 64);
+        uint8_t* const stage_base = smem + s * ((BN / 32) * BM * 64);
         long long out_row;
         int grp;
         bool row_ok;
@@ -444,44 +391,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // (the prefetch needs a second 32-register buffer: only where one CTA per SM leaves the registers free)
         constexpr bool PF = BN > 160;
         uint32_t raw[PF ? 2 : 1][32];
-        if (!ck && PF && hf < NCHUNK) tmem_ld32(taddr + hf * 32, raw[0]);
-        const int S = ck ? p.cluster_k : 1;
-        const int z = ck ? static_cast<int>(blockIdx.z) : 0;
+        if (PF && hf < NCHUNK) tmem_ld32(taddr + hf * 32, raw[0]);
 #pragma unroll
         for (int j = 0; j < MY_MAX; ++j) {
-            // without a cluster: chunk 2j + hf. In a cluster: the (2j + hf)-th chunk this CTA owns.
-            const int c = ck ? z + (2 * j + hf) * S : 2 * j + hf;
+            const int c = 2 * j + hf;
             if (c >= NCHUNK) break;
-            float v[32];
-            if (ck) {
-                // (0 + p0) + p1 + ...: the workspace path starts from zero, and 0 + (-0) is +0
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = 0.f;
-                const uint32_t mine = smem_u32(part + (static_cast<size_t>(c) * BM + r) * 32);
-                for (int zz = 0; zz < S; ++zz) {
-                    const uint32_t ra = dsmem_addr(mine, static_cast<uint32_t>(zz));
-                    float4 t[8];
-#pragma unroll
-                    for (int g = 0; g < 8; ++g) t[g] = ld_dsmem_f4(ra + 16 * (g ^ (r & 7)));
-#pragma unroll
-                    for (int g = 0; g < 8; ++g) {
-                        v[4 * g] += t[g].x; v[4 * g + 1] += t[g].y; v[4 * g + 2] += t[g].z; v[4 * g + 3] += t[g].w;
-                    }
-                }
-            } else {
-                if (!PF) tmem_ld32(taddr + c * 32, raw[0]);
-                tmem_wait_ld();
-                if (PF && j + 1 < MY_MAX && c + 2 < NCHUNK) tmem_ld32(taddr + (c + 2) * 32, raw[PF ? ((j + 1) & 1) : 0]);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
-            }
+            if (!PF) tmem_ld32(taddr + c * 32, raw[0]);
+            tmem_wait_ld();
+            if (PF && j + 1 < MY_MAX && c + 2 < NCHUNK) tmem_ld32(taddr + (c + 2) * 32, raw[PF ? ((j + 1) & 1) : 0]);
             const int n_base = n0 + c * 32;
             if (p.tma_store) {
                 if (n_base >= p.N) continue;                           // warp-uniform: the whole box is out of range
-                uint8_t* box = stage_base + (ck ? 2 * j + hf : c) * (BM * 64);    // cluster: one box per OWNED chunk
-                if (row_ok)
+                uint8_t* box = stage_base + c * (BM * 64);
+                if (row_ok) {
+                    float v[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
                     epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias_s + c * 32, rowbias_global, box + r * 64,
                                              (r >> 1) & 3);
+                }
                 fence_proxy_async();
                 asm volatile("bar.sync %0, 128;\n" ::"r"(2 + hf) : "memory");   // the four warps of this chunk parity
                 if (q == 0 && lane == 0) {
@@ -492,7 +420,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 continue;
             }
             if (row_ok && n_base < p.N) {
-                if (p.splitk > 1 && !ck) {
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[PF ? (j & 1) : 0][i]);
+                if (p.splitk > 1) {
                     const int owner = static_cast<int>(out_row / p.rows_per_owner);
                     float* ws = p.ws_peer[owner] + (static_cast<long long>(p.z_base + blockIdx.z) * p.rows_per_owner +
                                                     (out_row - static_cast<long long>(owner) * p.rows_per_owner)) * p.N + n_base;
@@ -508,7 +439,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }   // sub-tiles
         if (p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
     }
-    if (ck) cluster_sync_all();                   // every CTA has read the parked accumulators: all may exit
 
     if (dbg && threadIdx.x == 64) dbg[4] = clock64() - t_start;       // epilogue done
     // ---- teardown -----------------------------------------------------------------------------
@@ -641,23 +571,7 @@ static int launch_gemm_mt(const CUtensorMap& tmA, const CUtensorMap& tmA2, const
     constexpr int smem = STAGES * (MT * BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 32 + MT * BN * 4 + 1024;
     static_assert(smem <= 227 * 1024, "stage count does not fit shared memory");
     if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, STAGES, T, EPI, MT>), smem)) return -1;
-    if (p.cluster_k > 1) {
-        cudaLaunchConfig_t cfg{};
-        cfg.gridDim = grid;
-        cfg.blockDim = dim3(GEMM_THREADS);
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 1;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = static_cast<unsigned>(p.cluster_k);
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES, T, EPI, MT>, tmA, tmA2, tmB, p));
-    } else {
-        AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI, MT>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
-    }
+    AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI, MT>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
     ab_count_launch(1);
     return 0;
 }
@@ -665,22 +579,11 @@ static int launch_gemm_mt(const CUtensorMap& tmA, const CUtensorMap& tmA2, const
 // STAGES is the depth for one 128-row tile per CTA; the two-tile variant exists for BN = 256 only (three 64 KB stages).
 // At BN <= 160 two co-resident CTAs already overlap each other's epilogue and loads: the ZeroScope convs measured
 // 1137-1236 TFLOP/s with one tile per CTA and 1121-1238 with two, so those widths keep one.
-// Deep-pipeline variants. When a launch has no more CTAs than the GPU has SMs (the low-resolution UNet levels, a row band
-// of patch parallelism), each SM holds ONE CTA and its main loop is a serial chain of K steps whose rate is
-// stages / (TMA round trip): with 3-4 stages a 128 x 64 step took ~0.35 us whatever the tile width (tuner, Kandinsky
-// 48x48x768 conv: 48.9 us on one GPU, still 38.2 us with an eighth of the rows). A lone CTA can have all 227 KB, so these
-// instantiations keep ~190 KB of operands in flight (10 / 8 / 7 / 6 / 5 stages). Same MMA order, same bytes. Only the
-// plain epilogue is instantiated (convs, QKV / output projections): the latency-bound layers have no activation.
-template <int BN> struct DeepStages { static constexpr int value = BN <= 32 ? 10 : BN <= 64 ? 8 : BN <= 96 ? 7 : BN <= 128 ? 6 : 5; };
-
 template <int BN, int STAGES, typename T, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
                        dim3 grid, cudaStream_t stream) {
     if constexpr (BN == 256) {
         if (p.mt == 2) return launch_gemm_mt<BN, 3, T, EPI, 2>(tmA, tmA2, tmB, p, grid, stream);
-    }
-    if constexpr (BN <= 160 && EPI == EPI_NONE) {
-        if (p.deep) return launch_gemm_mt<BN, DeepStages<BN>::value, T, EPI, 1>(tmA, tmA2, tmB, p, grid, stream);
     }
     return launch_gemm_mt<BN, STAGES, T, EPI, 1>(tmA, tmA2, tmB, p, grid, stream);
 }
@@ -723,22 +626,6 @@ extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, c
 #else
 extern "C" int ab_gemm_main_bf16(int main_epi, int bn, const CUtensorMap* tmA, const CUtensorMap* tmA2, const CUtensorMap* tmB,
                                  const void* params, unsigned gx, unsigned gy, unsigned gz, void* stream);
-
-// Split-K through the fp32 workspace + reduce kernel (default) or inside a thread-block cluster (AB_SPLITK_CLUSTER=1, or
-// ab_gemm_set_cluster_splitk(1) at run time: the tests compare the two paths bit for bit). Measured on B200
-// (scripts/phase_splitk.py, 48x48x768 conv, BN 256): the cluster form saves the second launch and the HBM round trip
-// but its DSMEM reads cost ~4 us per split and its two cluster barriers hold every SM of the cluster until the slowest
-// CTA is through — 78 vs 76 us at two splits, 131 vs 87 at four, 173 vs 114 at six. It stays opt-in until the
-// cross-SM reads are restructured (more loads in flight per thread).
-static int g_cluster_splitk = -1;
-extern "C" int ab_gemm_cluster_splitk_enabled(void) {
-    if (g_cluster_splitk < 0) {
-        const char* e = getenv("AB_SPLITK_CLUSTER");
-        g_cluster_splitk = (e && e[0] == '1') ? 1 : 0;
-    }
-    return g_cluster_splitk;
-}
-extern "C" void ab_gemm_set_cluster_splitk(int on) { g_cluster_splitk = on ? 1 : 0; }
 
 static long long* g_gemm_dbg = nullptr;
 // Profiling aid: point at a device buffer of >= 8 * grid_size int64 to receive per-CTA phase cycle counts.
@@ -825,8 +712,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         }
         p.workspace = p.ws_peer[d->rs_rank];
     }
-    p.cluster_k = (ab_gemm_cluster_splitk_enabled() && splitk > 1 && splitk <= 8 && !rs) ? splitk : 0;
-    if (splitk > 1 && !p.cluster_k) AB_REQUIRE(p.workspace, "split-K needs a workspace");
+    if (splitk > 1) AB_REQUIRE(p.workspace, "split-K needs a workspace");
     if (ag) {
         AB_REQUIRE(!a->conv && a->K2 == 0, "all-gather mode: linear GEMM without virtual concat");
         AB_REQUIRE(d->nsrc == 2 || d->nsrc == 4 || d->nsrc == 8, "all-gather mode: 2/4/8 sources");
@@ -881,7 +767,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
 
     static const bool tma_store_on = [] { const char* e = getenv("AB_TMA_STORE"); return !(e && e[0] == '0'); }();
     p.tma_store = 0;
-    if (tma_store_on && !a->geglu && (splitk <= 1 || p.cluster_k) && !rs && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0) {
+    if (tma_store_on && !a->geglu && splitk <= 1 && !rs && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0) {
         const uint64_t ld = (uint64_t)p.ldo * esz;
         if (a->conv) {
             uint64_t dims[4] = {(uint64_t)a->N, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
@@ -901,25 +787,22 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     const int n_tiles = (a->N + bn - 1) / bn;
     // two tiles per CTA: only for long main loops (the doubled epilogue is serial behind them: 512x512x128->128 with
     // 18 K steps got 20 % slower) on problems that still give every SM two waves
-    p.mt = (mt_on && !ag && !p.cluster_k && bn == 256 && tiles_m % 2 == 0 && p.chunks_per_split >= 24 &&
+    p.mt = (mt_on && !ag && bn == 256 && tiles_m % 2 == 0 && p.chunks_per_split >= 24 &&
             static_cast<long long>(tiles_m / 2) * n_tiles * grid_z >= 2LL * ab_sm_count()) ? 2 : 1;
     dim3 grid(tiles_m / p.mt, n_tiles, grid_z);
-    static const bool deep_on = [] { const char* e = getenv("AB_GEMM_DEEP"); return !(e && e[0] == '0'); }();
-    p.deep = (deep_on && p.mt == 1 && static_cast<long long>(grid.x) * grid.y * grid.z <= ab_sm_count() &&
-              p.chunks_per_split >= 12) ? 1 : 0;
     int epi = a->geglu ? EPI_GEGLU
             : a->act == ACT_NONE ? EPI_NONE
             : a->act == ACT_SILU ? EPI_SILU
             : a->act == ACT_GELU ? EPI_GELU
             : a->act == ACT_QUICK_GELU ? EPI_QGELU : EPI_ANY;
-    const int main_epi = (splitk > 1 && !p.cluster_k) ? EPI_NONE : epi;   // workspace split-K: the main kernel only stores fp32 partials
+    const int main_epi = splitk > 1 ? EPI_NONE : epi;     // with split-K the main kernel only stores fp32 partials
     int rc = 0;
     if (phase != 2) {
         if (a->dtype == AB_BF16) rc = ab_gemm_main_bf16(main_epi, bn, &tmA, &tmA2, &tmB, &p, grid.x, grid.y, grid.z, stream_);
         else rc = gemm_main_t<__half>(main_epi, bn, tmA, tmA2, tmB, p, grid, stream);
     }
     if (rc) return rc;
-    if (splitk > 1 && phase != 1 && !p.cluster_k) {
+    if (splitk > 1 && phase != 1) {
         if (rs) { p.M = p.rows_per_owner; p.splitk = 8; }      // owners reduce their own row band
         // one thread per (row, 32-column chunk); 64-thread blocks keep many CTAs in flight for small M*N
         const long long work = static_cast<long long>(p.M) * ((p.N + 31) / 32);

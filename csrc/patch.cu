@@ -200,3 +200,30 @@ extern "C" int ab_sync_pingpong(unsigned int* my_flags, unsigned int* peer_flags
     ab_count_launch(1);
     return 0;
 }
+
+// ---- NVLS broadcast: one multimem.st per 16 bytes, the NVSwitch replicates it into every bound GPU's copy ------------
+// dst_mc is the MULTICAST mapping of a buffer (parallel/nvls.py). Stores only: the switch copies, it never reduces.
+namespace ab {
+__global__ void __launch_bounds__(256) multimem_copy_kernel(float4* __restrict__ dst_mc, const float4* __restrict__ src,
+                                                            long long n16) {
+    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < n16; i += static_cast<long long>(gridDim.x) * 256) {
+        const float4 v = src[i];
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst_mc + i), "f"(v.x), "f"(v.y),
+                     "f"(v.z), "f"(v.w)
+                     : "memory");
+    }
+}
+}  // namespace ab
+
+extern "C" int ab_multimem_copy(void* dst_mc, const void* src, long long nbytes, void* stream_) {
+    AB_REQUIRE(dst_mc && src && nbytes > 0 && nbytes % 16 == 0, "bad arguments");
+    AB_REQUIRE((reinterpret_cast<uintptr_t>(dst_mc) & 15) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0, "16-byte alignment required");
+    const long long n16 = nbytes / 16;
+    long long blocks = n16 / (256 * 8) + 1;
+    if (blocks > 148) blocks = 148;
+    ab::multimem_copy_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(
+        reinterpret_cast<float4*>(dst_mc), reinterpret_cast<const float4*>(src), n16);
+    AB_CHECK_CUDA(cudaGetLastError());
+    ab_count_launch(1);
+    return 0;
+}

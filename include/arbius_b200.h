@@ -93,12 +93,6 @@ typedef struct {
 } ab_gemm_dist_args;
 int ab_gemm_dist(const ab_gemm_args* args, const ab_gemm_dist_args* dist, int phase, void* stream);
 size_t ab_gemm_workspace_bytes(const ab_gemm_args* args);
-/* splitk > 1 can run as ONE launch (opt-in: 1 here or env AB_SPLITK_CLUSTER=1): the splitk CTAs of an output tile form
- * a thread-block cluster, park their fp32 accumulators in shared memory, and every CTA adds the parked accumulators of
- * the 32-column chunks it owns in split order through distributed shared memory before the epilogue. Bit-identical to
- * the default workspace + second-kernel path, which measured faster on B200 beyond two splits (see csrc/gemm_tc.cu). */
-int ab_gemm_cluster_splitk_enabled(void);
-void ab_gemm_set_cluster_splitk(int on);
 
 /* ---- K1 small-channel direct conv (conv_in / conv_out, Cin or Cout < 64) ------------------------ */
 /* x [N,H,W,Cin] -> out [N,Ho,Wo,Cout], pad = KH/2, stride 1 or 2. Weight layout by shape class:
@@ -159,6 +153,11 @@ typedef struct {
   unsigned int* local_site;
 } ab_patch_copy_args;
 int ab_patch_copy(const ab_patch_copy_args* args, void* stream);
+/* NVLS broadcast: copy nbytes (16-byte units) from src to the MULTICAST mapping dst_mc of a buffer bound on every GPU
+ * of the subset (parallel/nvls.py: cuMulticastCreate / cuMulticastBindMem); the NVSwitch replicates each multimem.st
+ * into every GPU's copy, so the producer's links carry each byte once. Stores only — values are copied, never reduced in
+ * the switch (its reduction order is the hardware's, and every exchange here feeds the CID). */
+int ab_multimem_copy(void* dst_mc, const void* src, long long nbytes, void* stream);
 /* GroupNorm of a row band in ONE launch (patch parallelism): the partial moments of this GPU's canonical shards go to
  * every GPU's array as self-validating 16-byte entries {mean, tick, M2, tick} (the flag travels inside the data: no
  * fence, no separate publish, no grid barrier), every GPU polls the entries of all 8 shards, merges them in canonical

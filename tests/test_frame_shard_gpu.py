@@ -52,7 +52,6 @@ def test_sharded_groupnorm_matches_undivided_bytes(world, shape):
 @pytest.mark.parametrize("world", [2, 4])
 def test_halo_temporal_conv_matches_undivided_bytes(world):
     ops = _ops()
-    from arbius_b200.ops import gemm as gemm_mod
     b, f, hw, c, n = 2, 8, 160, 128, 192
     torch.manual_seed(1)
     x = torch.randn(b, f, hw, c, device="cuda").half()
@@ -62,7 +61,7 @@ def test_halo_temporal_conv_matches_undivided_bytes(world):
     ref = ops.conv_temporal(x, w, bias, residual=res)
     fl = f // world
     zero = torch.zeros(b, 1, hw, c, dtype=x.dtype, device="cuda")
-    with gemm_mod.batch_scale(world):
+    with ops.batch_scale(world):
         for r in range(world):
             prev = x[:, r * fl - 1:r * fl] if r > 0 else zero
             nxt = x[:, (r + 1) * fl:(r + 1) * fl + 1] if r < world - 1 else zero
@@ -116,7 +115,6 @@ def test_peer_copy2d_strided_and_zero_fill():
 def test_halo_conv3x3_row_bands_match_undivided_bytes(world, concat):
     """Patch parallelism's conv: every rank holds a row band of the image plus one halo row above and below."""
     ops = _ops()
-    from arbius_b200.ops import gemm as gemm_mod
     b, h, wd, c, n = 2, 32, 32, 128, 192
     torch.manual_seed(3)
     x = torch.randn(b, h, wd, c, device="cuda").half()
@@ -132,7 +130,7 @@ def test_halo_conv3x3_row_bands_match_undivided_bytes(world, concat):
         top = t[:, r * hl - 1:r * hl] if r > 0 else z
         bot = t[:, (r + 1) * hl:(r + 1) * hl + 1] if r < world - 1 else z
         return torch.cat([top, t[:, r * hl:(r + 1) * hl], bot], 1).contiguous()
-    with gemm_mod.batch_scale(world):
+    with ops.batch_scale(world):
         for r in range(world):
             got = ops.conv3x3(band(x, r), w, bias, x2=band(x2, r) if concat else None, act="silu", halo=True)
             assert torch.equal(got, ref[:, r * hl:(r + 1) * hl]), f"rank {r}"

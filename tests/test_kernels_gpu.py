@@ -305,38 +305,3 @@ def test_groupnorm_fused_kernel_matches_two_kernel_path_bitwise():
         torch.cuda.synchronize()
         assert torch.equal(y, y2), (n, hw, c)
 
-
-@pytest.mark.gpu
-@pytest.mark.parametrize("splitk", [2, 3, 4, 6, 8])
-def test_cluster_splitk_equals_workspace_splitk_bit_for_bit(splitk):
-    """Split-K through a thread-block cluster (accumulators parked in shared memory, summed by the first CTA through
-    DSMEM) must give the bytes of the fp32-workspace + reduce-kernel path: same partial sums, same order."""
-    import ctypes as C
-
-    from arbius_b200 import ops
-    lib = ops.native.load()
-    lib.ab_gemm_set_cluster_splitk.argtypes = [C.c_int]
-    torch.manual_seed(splitk)
-    cases = []
-    x = torch.randn(2, 12, 12, 1536, device="cuda").half()
-    w = ops.pack_conv_weight((torch.randn(1536, 1536, 3, 3, device="cuda") * 0.02).half())
-    b = torch.randn(1536, device="cuda").half()
-    res = torch.randn(2, 12, 12, 1536, device="cuda").half()
-    cases.append(lambda bn: ops.conv3x3(x, w, b, residual=res, act="silu", splitk=splitk, block_n=bn))
-    xl = torch.randn(300, 2048, device="cuda").half()
-    wl = (torch.randn(640, 2048, device="cuda") * 0.03).half()
-    bl = torch.randn(640, device="cuda").half()
-    cases.append(lambda bn: ops.gemm(xl, wl, bl, splitk=splitk, block_n=bn))
-    xg = torch.randn(256, 1280, device="cuda").half()
-    wg, bg = ops.pack_geglu_weight((torch.randn(2 * 640, 1280, device="cuda") * 0.03).half(), torch.randn(1280, device="cuda").half())
-    cases.append(lambda bn: ops.gemm(xg, wg, bg, geglu=True, splitk=splitk, block_n=bn if bn % 32 == 0 else 64))
-    try:
-        for fn in cases:
-            for bn in (32, 64, 96, 128, 160, 256):
-                lib.ab_gemm_set_cluster_splitk(0)
-                want = fn(bn)
-                lib.ab_gemm_set_cluster_splitk(1)
-                got = fn(bn)
-                assert torch.equal(got, want), f"splitk={splitk} bn={bn}"
-    finally:
-        lib.ab_gemm_set_cluster_splitk(0)              # the library default

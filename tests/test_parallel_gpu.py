@@ -114,3 +114,17 @@ def test_frame_parallel_predictor_in_one_process_matches_single_gpu_bytes():
     assert fp(dict(inp)) == want
     assert fp(dict(inp)) == want                         # graph replay
     assert fp(dict(inp, seed=6)) != want
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_patch_parallel_kandinsky_matches_single_gpu_bytes():
+    """One image over 2/4/8 GPUs in row bands (BASELINE config 3): GroupNorm with the moments exchanged inside the
+    kernel, halo convs whose producer warp waits for the neighbours' flag, attention over every band's K/V — operator by
+    operator and through the whole tiny Kandinsky 2.1 pipeline (graph replay included) the bytes equal the 1-GPU run."""
+    n = min(torch.cuda.device_count(), 8)
+    n = max(p for p in (2, 4, 8) if p <= n)
+    r = _torchrun("mp_patch_parallel.py", n, 29619, timeout=900)
+    sys.stdout.write(r.stdout[-3000:])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "bit-identical=False" not in r.stdout and "patch-parallel P=" in r.stdout
