@@ -317,7 +317,9 @@ __device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 // Spin until every rank in `mask` has published a value >= tick in this GPU's copy of the site. Bounded: a protocol
 // bug or a dead peer traps (~60 s) instead of hanging the box.
-__device__ __forceinline__ void sync_wait_flags(const unsigned int* site, unsigned int mask, unsigned int tick) {
+// (not inlined: the spin loop with its timeout report would otherwise raise the register count of every kernel that
+// can wait, and the tcgen05 GEMM runs two CTAs per SM on a 96-register budget)
+__device__ __noinline__ void sync_wait_flags(const unsigned int* site, unsigned int mask, unsigned int tick) {
     while (mask) {
         const int r = __ffs(mask) - 1;
         mask &= mask - 1;
