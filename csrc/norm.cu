@@ -555,6 +555,10 @@ struct GnPatch {
     unsigned int* done_sites[8];
     unsigned int* done_local;
     int world, rank, dry;
+    // single-GPU use (ab_groupnorm): the tick is a counter in the caller's workspace that the last CTA of every launch
+    // advances, so consecutive launches on a stream never see each other's entries as current; no flags go anywhere
+    unsigned int* self_tick;
+    unsigned int* self_ticket;
 };
 
 __device__ __forceinline__ void st_ll16(uint4* p, uint4 v) {
@@ -600,14 +604,14 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
     const int items_per_img = ns * p.sub;
     const int total_items = p.n * items_per_img;
     const bool use_cache = cache_rows > 0;
-    const unsigned int tick = x.tick ? *x.tick : 0u;
+    const unsigned int tick = x.self_tick ? *x.self_tick + 1u : (x.tick ? *x.tick : 0u);
     const int shard_len = p.hw / ns;                       // rows of one canonical shard (hw % ns == 0)
 
     auto item_rows = [&](int item, int& n, int& shard, int& sb, int& r0, int& r1) {
         n = item / items_per_img;
         const int rem = item - n * items_per_img;
         shard = rem / p.sub; sb = rem - shard * p.sub;
-        const int s_begin = shard * shard_len;
+        const int s_begin = shard * shard_len;             // (callers guarantee hw % ns == 0)
         r0 = s_begin + static_cast<int>((static_cast<long long>(sb) * shard_len) / p.sub);
         r1 = s_begin + static_cast<int>((static_cast<long long>(sb + 1) * shard_len) / p.sub);
     };
@@ -794,6 +798,17 @@ __global__ void __launch_bounds__(GN_THREADS) gn_patch_kernel(const GnParams p, 
         }
         cached += r1 - r0;
     }
+    if (x.self_tick) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned int ticket = atomicAdd(x.self_ticket, 1u);
+            if (ticket == gridDim.x - 1) {        // every CTA has read what it needs: the next launch may use tick + 1
+                *x.self_ticket = 0;
+                *x.self_tick = tick;
+            }
+        }
+    }
     if (x.done_local && !x.dry) {
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -908,6 +923,36 @@ extern "C" int ab_groupnorm(const ab_groupnorm_args* a, void* stream_) {
     const int max_item_rows = ((a->hw + GN_SHARDS - 1) / GN_SHARDS + p.sub - 1) / p.sub + 1;
     const long long need_rows = static_cast<long long>(items_per_cta) * max_item_rows;
     const long long cap_rows = (200LL * 1024 - static_cast<long long>(smem)) / (static_cast<long long>(C) * 2);
+    // Flag-in-data form of the one-launch kernel (gn_patch_kernel with a single rank): every CTA stores its moments as
+    // self-validating entries and polls the ones it needs, which replaces the grid barrier between the statistics and
+    // the apply phase. Same items, same arithmetic, same merge order: the bytes are gn_fused_kernel's.
+    static const bool ll_on = [] { const char* e = getenv("AB_GN_LL"); return !(e && e[0] == '0'); }();
+    if (fused_on && ll_on && need_rows <= cap_rows && a->hw % GN_SHARDS == 0 && a->n <= 56) {
+        if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_patch_kernel<__half>), 200 * 1024)) return -1;
+        if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_patch_kernel<__nv_bfloat16>), 200 * 1024)) return -1;
+        GnPatch x{};
+        x.part_peers[0] = reinterpret_cast<uint4*>(p.partials);
+        x.world = 1; x.rank = 0;
+        x.self_ticket = p.counters + a->n + 2;
+        x.self_tick = p.counters + a->n + 3;
+        p.ns_local = GN_SHARDS; p.shard_base = 0;
+        const int cache_rows = static_cast<int>(need_rows);
+        const size_t smem_f = smem + static_cast<size_t>(cache_rows) * C * 2;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(grid_f);
+        cfg.blockDim = dim3(GN_THREADS);
+        cfg.dynamicSmemBytes = smem_f;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeCooperative;
+        attr[0].val.cooperative = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (a->dtype == AB_BF16) AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__nv_bfloat16>, p, x, cache_rows));
+        else AB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gn_patch_kernel<__half>, p, x, cache_rows));
+        ab_count_launch(1);
+        return 0;
+    }
     if (fused_on && need_rows <= cap_rows) {
         if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_fused_kernel<__half>), 200 * 1024)) return -1;
         if (ab_ensure_max_smem(reinterpret_cast<const void*>(gn_fused_kernel<__nv_bfloat16>), 200 * 1024)) return -1;
