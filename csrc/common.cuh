@@ -319,7 +319,7 @@ __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.pr
 // bug or a dead peer traps (~60 s) instead of hanging the box.
 // (not inlined: the spin loop with its timeout report would otherwise raise the register count of every kernel that
 // can wait, and the tcgen05 GEMM runs two CTAs per SM on a 96-register budget)
-__device__ __noinline__ void sync_wait_flags(const unsigned int* site, unsigned int mask, unsigned int tick) {
+static __device__ __noinline__ void sync_wait_flags(const unsigned int* site, unsigned int mask, unsigned int tick) {
     while (mask) {
         const int r = __ffs(mask) - 1;
         mask &= mask - 1;
