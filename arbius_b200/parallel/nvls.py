@@ -76,9 +76,10 @@ class MulticastBuffer:
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         dev = torch.cuda.current_device()
         torch.zeros(1, device="cuda")                      # make sure the primary context exists and is current
+        FD = cu.CUmemAllocationHandleType.CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR
         mprop = cu.CUmulticastObjectProp()
         mprop.numDevices = self.world
-        mprop.handleTypes = cu.CUmemAllocationHandleType.CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR
+        mprop.handleTypes = FD
         mprop.flags = 0
         mprop.size = int(nbytes)
         gran = _ok(cu.cuMulticastGetGranularity(mprop, cu.CUmulticastGranularity_flags.CU_MULTICAST_GRANULARITY_RECOMMENDED),
@@ -96,7 +97,7 @@ class MulticastBuffer:
         if self.rank == 0:
             self.mc = _ok(cu.cuMulticastCreate(mprop), "cuMulticastCreate")
             if self.world > 1:
-                fd = _ok(cu.cuMemExportToShareableHandle(self.mc, mprop.handleTypes, 0), "export multicast handle")
+                fd = _ok(cu.cuMemExportToShareableHandle(self.mc, FD, 0), "export multicast handle")
                 srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
                 if os.path.exists(path):
                     os.unlink(path)
@@ -116,7 +117,7 @@ class MulticastBuffer:
             cli.connect(path)
             fd = _recv_fd(cli)
             cli.close()
-            self.mc = _ok(cu.cuMemImportFromShareableHandle(fd, mprop.handleTypes), "import multicast handle")
+            self.mc = _ok(cu.cuMemImportFromShareableHandle(fd, FD), "import multicast handle")
             os.close(fd)
         _ok(cu.cuMulticastAddDevice(self.mc, dev), "cuMulticastAddDevice")
         if self.world > 1:
@@ -126,7 +127,7 @@ class MulticastBuffer:
         aprop.type = cu.CUmemAllocationType.CU_MEM_ALLOCATION_TYPE_PINNED
         aprop.location.type = cu.CUmemLocationType.CU_MEM_LOCATION_TYPE_DEVICE
         aprop.location.id = dev
-        aprop.requestedHandleTypes = cu.CUmemAllocationHandleType.CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR
+        aprop.requestedHandleTypes = FD
         self.mem = _ok(cu.cuMemCreate(self.nbytes, aprop, 0), "cuMemCreate")
         _ok(cu.cuMulticastBindMem(self.mc, 0, self.mem, 0, self.nbytes, 0), "cuMulticastBindMem")
         acc = cu.CUmemAccessDesc()
