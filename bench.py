@@ -511,7 +511,7 @@ def main() -> int:
     ap.add_argument("--headline-only", action="store_true", help="skip the comparator, ZeroScope, Kandinsky and latency blocks")
     ap.add_argument("--latency-mode", action="store_true", help="(kept for compatibility: latency mode is on by default at N >= 2)")
     ap.add_argument("--no-latency-mode", action="store_true")
-    ap.add_argument("--task-batch", type=int, default=3,
+    ap.add_argument("--task-batch", type=int, default=4,
                     help="independent tasks per graph replay (anythingv3 native only); bytes per task do not change")
     args = ap.parse_args()
     if args.impl == "reference":
