@@ -14,6 +14,7 @@
 // tiles in the same order with some of them living in peer memory.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../include/arbius_b200.h"
 #include "common.cuh"
@@ -43,7 +44,10 @@ struct AttnParams {
     const unsigned int* tick;        // cross-GPU flags: wait for source s (s != self_rank) before the first load from it
     const unsigned int* wait_site;
     int self_rank;
+    long long* dbg;                  // profiling aid (ab_attn_set_debug): CTA (0,0,0) of the v3 kernel records a timeline
 };
+
+static long long* g_attn_dbg = nullptr;
 
 template <int NCH, typename T>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
@@ -99,7 +103,7 @@ flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     pdl_launch_dependents();
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {   // single-lane region the compiler can see: operands stay in uniform registers
             mbar_expect_tx(q_full, QB);
 #pragma unroll
             for (int c = 0; c < NCH; ++c) tma_load_4d(sQ + c * CHUNK_BYTES, &tmQ, q_full, c * 64, h, q0, b);
@@ -116,7 +120,7 @@ flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one()) {   // single-lane region the compiler can see: operands stay in uniform registers
             const uint32_t idesc_qk = make_idesc_f16(ATT_BM, ATT_BN, DT<T>::kBf16, false, false);
             const uint32_t idesc_pv = make_idesc_f16(ATT_BM, DP, DT<T>::kBf16, false, true);
             const uint32_t q_addr = smem_u32(sQ);
@@ -288,6 +292,29 @@ flash_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
 }
 
 #include "attention_v2.cuh"
+#include "attention_v3.cuh"
+
+// Profiling aid: a device buffer of >= 4096 int64. CTA (0,0,0) of flash_attn3_kernel writes clock64() stamps for its
+// first 32 KV tiles: [0..) MMA thread {P_A seen, A issued, P_B seen, B issued}, [1024..) softmax warp of tile A
+// {S ready, exps done}, [2048..) the same for tile B. scripts/attn_timeline.py prints it.
+extern "C" void ab_attn_set_debug(long long* buf) { ab::g_attn_dbg = buf; }
+// AB_ATTN_V=2 selects the previous kernel (P through shared memory, two reads of S) for A/B measurements.
+static int attn_version() {
+    static const int v = [] { const char* e = getenv("AB_ATTN_V"); return e ? atoi(e) : 3; }();
+    return v;
+}
+template <typename T, typename KV>
+static int launch_attn_pp(const CUtensorMap& tq, const KV& kv, const AttnParams& p, cudaStream_t stream) {
+    return attn_version() == 2 ? launch_attn2_multi<T, KV>(tq, kv, p, stream) : launch_attn3_multi<T, KV>(tq, kv, p, stream);
+}
+template <typename T>
+static int launch_attn_pp1(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
+                           cudaStream_t stream) {
+    KvMaps<1> kv;
+    kv.k[0] = tk;
+    kv.v[0] = tv;
+    return launch_attn_pp<T, KvMaps<1>>(tq, kv, p, stream);
+}
 
 template <int NCH, typename T>
 static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
@@ -315,6 +342,7 @@ extern "C" int ab_flash_attn(const ab_attn_args* a, void* stream_) {
     const int D = a->head_dim;
     const int nch = (D + 63) / 64;
     AttnParams p{};
+    p.dbg = g_attn_dbg;
     p.out = a->out; p.batch = a->batch; p.heads = a->heads; p.lq = a->lq; p.lk = a->lk; p.head_dim = D;
     p.o_bs = a->o_bs; p.o_ls = a->o_ls;
     const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
@@ -331,7 +359,7 @@ extern "C" int ab_flash_attn(const ab_attn_args* a, void* stream_) {
     if (mk(&tk, a->k, a->lk, a->k_bs, a->k_ls)) return -1;
     if (mk(&tv, a->v, a->lk, a->v_bs, a->v_ls)) return -1;
 #define AB_ATT(T)                                                      \
-    (nch == 1 ? ((a->lq > 128 || (a->causal & 2)) ? launch_attn2<T>(tq, tk, tv, p, stream) : launch_attn<1, T>(tq, tk, tv, p, stream)) \
+    (nch == 1 ? ((a->lq > 128 || (a->causal & 2)) ? launch_attn_pp1<T>(tq, tk, tv, p, stream) : launch_attn<1, T>(tq, tk, tv, p, stream)) \
      : nch == 2 ? launch_attn<2, T>(tq, tk, tv, p, stream)             \
                 : launch_attn<3, T>(tq, tk, tv, p, stream))
     return a->dtype == AB_BF16 ? AB_ATT(__nv_bfloat16) : AB_ATT(__half);
@@ -352,6 +380,7 @@ extern "C" int ab_flash_attn_multi(const ab_attn_args* a, const void* const* k_p
     AB_REQUIRE(!a->causal, "causal masking is not supported in the multi-source path");
     const int D = a->head_dim;
     AttnParams p{};
+    p.dbg = g_attn_dbg;
     p.out = a->out; p.batch = a->batch; p.heads = a->heads; p.lq = a->lq; p.lk = nsrc * lk_per_src; p.head_dim = D;
     p.o_bs = a->o_bs; p.o_ls = a->o_ls;
     const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
@@ -373,7 +402,7 @@ extern "C" int ab_flash_attn_multi(const ab_attn_args* a, const void* const* k_p
             if (mk(&kv.k[s], k_ptrs[s], lk_per_src, a->k_bs, a->k_ls)) return -1;             \
             if (mk(&kv.v[s], v_ptrs[s], lk_per_src, a->v_bs, a->v_ls)) return -1;             \
         }                                                                                     \
-        return launch_attn2_multi<T, KvMaps<N>>(tq, kv, p, stream);                                   \
+        return launch_attn_pp<T, KvMaps<N>>(tq, kv, p, stream);                                   \
     }
 #define AB_ATT_MULTI_T(T)                                  \
     switch (nsrc) {                                        \
@@ -401,6 +430,7 @@ extern "C" int ab_flash_attn_segs(const ab_attn_segs_args* a, void* stream_) {
     AB_REQUIRE(!a->wait_site || a->tick, "wait_site needs tick");
     const int D = a->head_dim;
     AttnParams p{};
+    p.dbg = g_attn_dbg;
     p.out = a->out; p.batch = a->batch; p.heads = a->heads; p.lq = a->lq; p.head_dim = D;
     p.o_bs = a->o_bs; p.o_ls = a->o_ls;
     const float scale = a->scale > 0.f ? a->scale : 1.0f / sqrtf(static_cast<float>(D));
@@ -432,6 +462,6 @@ extern "C" int ab_flash_attn_segs(const ab_attn_segs_args* a, void* stream_) {
         kv.big[0] = kv.big[1];
     }
     kv.small[0] = kv.small[1];
-    if (a->dtype == AB_BF16) return launch_attn2_multi<__nv_bfloat16, SegMaps>(tq, kv, p, stream);
-    return launch_attn2_multi<__half, SegMaps>(tq, kv, p, stream);
+    if (a->dtype == AB_BF16) return launch_attn_pp<__nv_bfloat16, SegMaps>(tq, kv, p, stream);
+    return launch_attn_pp<__half, SegMaps>(tq, kv, p, stream);
 }

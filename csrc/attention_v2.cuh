@@ -124,7 +124,7 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     pdl_launch_dependents();
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {   // single-lane region the compiler can see: operands stay in uniform registers
             mbar_expect_tx(q_full, (b_active ? 2 : 1) * CHUNK_BYTES);
             tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
             if (b_active) tma_load_4d(sQ + CHUNK_BYTES, &tmQ, q_full, 0, h, q0 + 128, b);
@@ -182,7 +182,7 @@ flash_attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one()) {   // single-lane region the compiler can see: operands stay in uniform registers
             const uint32_t idesc_qk = make_idesc_f16(ATT_BM, ATT_BN, DT<T>::kBf16, false, false);
             const uint32_t idesc_pv = make_idesc_f16(ATT_BM, DP, DT<T>::kBf16, false, true);
             auto issue_qk = [&](int t, int j) {

@@ -156,6 +156,11 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
     d |= static_cast<uint64_t>(layout_type & 7) << 61;
     return d;
 }
+// Descriptor for another address with the same strides and swizzle: `tmpl` is make_smem_desc(0, ...). One OR on the
+// low word, so a loop over K steps / stages keeps the rest in (uniform) registers.
+__device__ __forceinline__ uint64_t smem_desc_at(uint64_t tmpl, uint32_t saddr) {
+    return tmpl | static_cast<uint64_t>((saddr >> 4) & 0x3FFF);
+}
 constexpr uint32_t kSwizzle128 = 2, kSwizzle64 = 4, kSwizzle32 = 6, kSwizzleNone = 0;
 
 // Instruction descriptor for kind::f16 (fp16/bf16 in, fp32 accumulate).
@@ -226,6 +231,14 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
         "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
         "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
         "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};\n" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
         : "memory");
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }

@@ -14,6 +14,7 @@
 // Split-K is a fixed, caller-chosen factor with an in-order second pass: results never depend on
 // scheduling, grid size or GPU count.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <unordered_map>
@@ -37,6 +38,7 @@ struct GemmParams {
     const void* residual;
     float* workspace;
     long long* dbg;             // optional per-CTA phase timestamps (debug/profiling only)
+    int stages;                 // pipeline depth of this launch (set by launch_gemm_mt: deep for grids of one wave)
     int M, N, Nout;
     int k1_chunks, k2_chunks;   // 64-wide chunks from source 1 / source 2 (per tap in conv mode)
     int taps;                   // 1 (linear) or 9 (conv)
@@ -185,12 +187,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "UMMA N for M=128; epilogue reads 32-column chunks");
     static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-byte alignment");
     static_assert(MT * (BN / 32) * BM * 64 <= STAGES * STAGE_BYTES, "output staging boxes reuse the pipeline stages");
+    // STAGES is the smallest depth this instantiation runs with (what fits twice on an SM); p.stages >= STAGES is the
+    // depth of THIS launch: a grid of at most one CTA per SM takes all the shared memory, because its K loop is paced
+    // by (TMA round trip) / depth, ~500 cycles per 64-deep step at depth 3-4 whatever the tile width.
+    const int stages = p.stages;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-    uint64_t* empty_bar = full_bar + STAGES;
-    uint64_t* acc_bar = empty_bar + STAGES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + stages * STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + stages;
+    uint64_t* acc_bar = empty_bar + stages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
     float* sbias = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot) + 4 + 15) & ~uintptr_t(15));  // [MT][BN]
 
@@ -229,7 +235,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         if (p.k2_chunks) tma_prefetch_desc(&tmA2);
-        for (int s = 0; s < STAGES; ++s) {
+        for (int s = 0; s < stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
@@ -248,7 +254,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     if (warp == 0) {
         // ================= TMA producer =================
-        if (lane == 0) {
+        // ONE lane chosen by elect.sync runs the whole loop. The compiler then knows the region is single-lane and keeps
+        // addresses, coordinates and descriptors in uniform registers. Under `if (lane == 0)` it cannot, and moves every
+        // UTMALDG / UTCHMMA operand out of a "divergent" context with an ELECT / R2UR / BRA.U.ANY loop (~100 cycles per
+        // instruction); a warp-uniform loop with `if (leader)` inside pays ~230 cycles per iteration for the branch and
+        // the reconvergence (scripts/micro/gemm_loop.cu: 470-500 -> 369 cycles per K step).
+        if (elect_one()) {
             if (p.sync_wait) {
                 // only a tile that touches a halo row has to wait for the neighbour that fills it: interior tiles start
                 // at once and hide the hand-off's NVLink latency
@@ -268,13 +279,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             int stage = 0;
             uint32_t phase = 0;
+            // (tap, channel chunk) advance by counting: no division in the loop
+            int tap = kc_begin / chunks_per_tap;
+            int cc = kc_begin - tap * chunks_per_tap;
             for (int kc = kc_begin; kc < kc_end; ++kc) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * STAGE_BYTES;
                 uint8_t* sb = sa + A_BYTES;
                 mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
-                const int tap = kc / chunks_per_tap;
-                const int cc = kc - tap * chunks_per_tap;
                 const bool second = cc >= p.k1_chunks;
                 const CUtensorMap* ma = second ? &tmA2 : &tmA;
                 const int c0 = (second ? cc - p.k1_chunks : cc) * BK;
@@ -296,36 +308,41 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     }
                 }
                 tma_load_2d(sb, &tmB, &full_bar[stage], kc * BK, n0);
-                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+                if (++cc == chunks_per_tap) { cc = 0; ++tap; }
             }
         }
+        __syncwarp();
     } else if (warp == 1) {
-        // ================= MMA issuer (one thread) =================
-        if (lane == 0) {
+        // ================= MMA issuer (one elected lane runs the loop, see the producer) =================
+        if (elect_one()) {
             constexpr uint32_t idesc = make_idesc_f16(BM, BN, DT<T>::kBf16, false, false);
+            const uint64_t desc0 = make_smem_desc(0, 16, 1024, kSwizzle128);
+            const uint32_t smem_base = smem_u32(smem);
             int stage = 0;
             uint32_t phase = 0;
             for (int kc = kc_begin; kc < kc_end; ++kc) {
                 mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
                 if (dbg && kc == kc_begin) dbg[1] = clock64() - t_start;   // first operands landed
-                const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+                const uint32_t sa = smem_base + stage * STAGE_BYTES;
                 const uint32_t sb = sa + A_BYTES;
 #pragma unroll
                 for (int k = 0; k < BK / UK; ++k) {
-                    const uint64_t bdesc = make_smem_desc(sb + k * UK * 2, 16, 1024, kSwizzle128);
+                    const uint64_t bdesc = smem_desc_at(desc0, sb + k * UK * 2);
 #pragma unroll
                     for (int s = 0; s < MT; ++s) {
-                        const uint64_t adesc = make_smem_desc(sa + s * A1_BYTES + k * UK * 2, 16, 1024, kSwizzle128);
+                        const uint64_t adesc = smem_desc_at(desc0, sa + s * A1_BYTES + k * UK * 2);
                         umma_ss(tmem_base + s * ACC_COLS, adesc, bdesc, idesc, (kc > kc_begin || k > 0) ? 1u : 0u);
                     }
                 }
                 umma_commit(&empty_bar[stage]);   // frees this smem stage once the MMAs have read it
-                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                if (++stage == stages) { stage = 0; phase ^= 1; }
             }
             umma_commit(acc_bar);                 // accumulator complete
             if (dbg) dbg[2] = clock64() - t_start;                     // all MMAs issued
         }
+        __syncwarp();
     } else {
         // ================= epilogue warps =================
         const int q = warp & 3;                   // TMEM lane quarter this warp may read
@@ -565,13 +582,29 @@ static int auto_block_n(int M_tiles, int N, bool geglu) {
     return best;
 }
 
+constexpr int gemm_smem_bytes(int stages, int stage_bytes, int bias_floats) {
+    return stages * stage_bytes + (2 * stages + 1) * 8 + 32 + bias_floats * 4 + 1024;
+}
+constexpr int gemm_deepest(int at_least, int stage_bytes, int bias_floats) {
+    int st = at_least;
+    while (st < 12 && gemm_smem_bytes(st + 1, stage_bytes, bias_floats) <= 227 * 1024) ++st;
+    return st;
+}
+
 template <int BN, int STAGES, typename T, int EPI, int MT>
 static int launch_gemm_mt(const CUtensorMap& tmA, const CUtensorMap& tmA2, const CUtensorMap& tmB, const GemmParams& p,
                           dim3 grid, cudaStream_t stream) {
-    constexpr int smem = STAGES * (MT * BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 32 + MT * BN * 4 + 1024;
-    static_assert(smem <= 227 * 1024, "stage count does not fit shared memory");
-    if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, STAGES, T, EPI, MT>), smem)) return -1;
-    AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI, MT>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, p));
+    constexpr int kStage = MT * BM * BK * 2 + BN * BK * 2;
+    static_assert(gemm_smem_bytes(STAGES, kStage, MT * BN) <= 227 * 1024, "stage count does not fit shared memory");
+    constexpr int kDeep = gemm_deepest(STAGES, kStage, MT * BN);   // deepest pipeline one CTA per SM can hold
+    auto smem_for = [](int st) { return gemm_smem_bytes(st, kStage, MT * BN); };
+    static const int deep_mode = [] { const char* e = getenv("AB_GEMM_DEEP"); return e ? atoi(e) : 1; }();
+    const long long ctas = static_cast<long long>(grid.x) * grid.y * grid.z;
+    GemmParams q = p;
+    q.stages = (deep_mode && ctas <= ab_sm_count()) ? kDeep : STAGES;
+    const int smem = smem_for(q.stages);
+    if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, STAGES, T, EPI, MT>), smem_for(kDeep))) return -1;
+    AB_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, STAGES, T, EPI, MT>, grid, dim3(GEMM_THREADS), smem, stream, tmA, tmA2, tmB, q));
     ab_count_launch(1);
     return 0;
 }

@@ -27,7 +27,7 @@ extern "C" const char* ab_last_error(void) {
 }
 extern "C" void ab_count_launch(int n) { g_launches.fetch_add(static_cast<unsigned long long>(n), std::memory_order_relaxed); }
 extern "C" unsigned long long ab_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
-extern "C" int ab_version(void) { return 100; }
+extern "C" int ab_version(void) { return 200; }   // bumped whenever output bytes change (goldens are keyed by it): 200 = attention v3, re-tuned split-K
 
 // Programmatic dependent launch switch: off unless AB_PDL=1 in the environment; ab_set_pdl() overrides (A/B timing).
 // Measured on the 20-step AnythingV3 task inside one CUDA graph: 137.2 ms without, 139.5 ms with — graph edges

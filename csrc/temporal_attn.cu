@@ -91,7 +91,7 @@ temporal_attn_kernel(const __grid_constant__ TaMaps maps, const TaParams p) {
     pdl_launch_dependents();
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {   // single-lane region the compiler can see: operands stay in uniform registers
             mbar_expect_tx(ld_full, 3u * static_cast<uint32_t>(R) * 128u);
             for (int s = 0; s < p.nsrc; ++s) {
                 if constexpr (PM) {

@@ -1,5 +1,6 @@
 """Kernel micro-benchmarks (CUDA events, L2 flushed between iterations). Writes JSON lines to stdout."""
 import json
+import subprocess
 import sys
 
 import torch
@@ -9,6 +10,16 @@ sys.path.insert(0, ".")
 from arbius_b200 import ops  # noqa: E402
 
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+
+def sm_mhz():
+    """Instantaneous SM clock and throttle reasons (sampled right after a timed loop, while the GPU is still warm)."""
+    try:
+        out = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.active", "--format=csv,noheader,nounits",
+                              "-i", "0"], capture_output=True, text=True, timeout=10).stdout.strip().split(",")
+        return dict(sm_mhz=float(out[0]), sm_max_mhz=float(out[1]), reasons=out[2].strip())
+    except Exception:  # noqa: BLE001
+        return {}
 
 
 def timeit(fn, iters=20, warmup=5):
@@ -69,7 +80,9 @@ def main():
         xc = x.permute(0, 2, 1).reshape(n, c, hw, 1).contiguous(memory_format=torch.channels_last)
         tr = timeit(lambda: F.silu(F.group_norm(xc, 32, g, g, 1e-5)))
         rows.append(dict(op="gn_silu", shape=[n, hw, c], ms=t, gbs=2 * x.numel() * 2 / t / 1e6, torch_ms=tr))
+    clocks = sm_mhz()
     for r in rows:
+        r["clocks_at_end"] = clocks
         print(json.dumps(r))
 
 
