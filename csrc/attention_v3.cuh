@@ -133,26 +133,28 @@ flash_attn3_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             }
         }
     } else if (warp == 1) {
-        // ONE lane chosen by elect.sync runs the whole loop: the compiler then keeps descriptors and addresses in uniform
-        // registers. (Under `if (lane == 0)` it moved every UTCHMMA operand out of a "divergent" context with an
-        // ELECT / R2UR / BRA.U.ANY loop — ~100 cycles per MMA, 1280 cycles to issue one tile's twelve MMAs, which paced
-        // the whole kernel; a warp-uniform loop with `if (leader)` inside pays for a branch and a reconvergence per use.)
-        if (elect_one()) {
+        // The whole warp runs this control flow and the elected lane issues inside `if (leader)`: descriptors and addresses
+        // stay in uniform registers (under `if (lane == 0)` every UTCHMMA operand was moved out of a "divergent" context
+        // with an ELECT / R2UR / BRA.U.ANY loop: 1280 cycles to issue one tile's twelve MMAs, which paced the kernel).
+        // Measured alternatives (scripts/attn_timeline.py, 48x5x9216^2x64): the whole loop under one elected lane issues a
+        // tile in 440 cycles instead of 740 but the two softmax groups then fall into closer lock-step (7.38 vs 6.96 ms);
+        // software-pipelining the exponentials over chunks (7.54) and passing an explicit turn between the groups with
+        // named barriers (8.54 exclusive, 7.52 half-way) did not beat it either.
+        {
+            const bool leader = elect_one();
             const uint32_t idesc_qk = make_idesc_f16(ATT_BM, ATT_BN, DT<T>::kBf16, false, false);
             const uint32_t idesc_pv = make_idesc_f16(ATT_BM, DP, DT<T>::kBf16, false, true);
             const uint32_t sq_base = smem_u32(sQ), sk_base = smem_u32(sK), sv_base = smem_u32(sV);
-            const uint64_t dqk = make_smem_desc(0, 16, 1024, kSwizzle128);
-            const uint64_t dv = make_smem_desc(0, CHUNK_BYTES, 1024, kSwizzle128);
-            const int nks = DP / 16;
             auto issue_qk = [&](int t, int j) {
                 const uint32_t q_addr = sq_base + t * CHUNK_BYTES;
                 const uint32_t k_addr = sk_base + (j % A3_STAGES) * CHUNK_BYTES;
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks)
-                    if (ks < nks)
-                        umma_ss(tmem_base + static_cast<uint32_t>(t) * 128u, smem_desc_at(dqk, q_addr + ks * 32),
-                                smem_desc_at(dqk, k_addr + ks * 32), idesc_qk, ks > 0 ? 1u : 0u);
-                umma_commit(&s_full[t]);
+                if (leader) {
+                    for (int ks = 0; ks < DP / 16; ++ks)
+                        umma_ss(tmem_base + static_cast<uint32_t>(t) * 128u, make_smem_desc(q_addr + ks * 32, 16, 1024, kSwizzle128),
+                                make_smem_desc(k_addr + ks * 32, 16, 1024, kSwizzle128), idesc_qk, ks > 0 ? 1u : 0u);
+                    umma_commit(&s_full[t]);
+                }
+                __syncwarp();
             };
             auto wait_p = [&](int t, int j) {
                 mbar_wait(&p_full[t], j & 1);
@@ -162,11 +164,15 @@ flash_attn3_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 // A = P from tensor memory: 16 keys of a K step are 8 columns (two 16-bit values per column)
                 const uint32_t p_taddr = tmem_base + 384u + static_cast<uint32_t>(t) * 64u;
                 const uint32_t v_addr = sv_base + (j % A3_STAGES) * CHUNK_BYTES;
+                if (leader) {
 #pragma unroll
-                for (int ks = 0; ks < ATT_BN / 16; ++ks)
-                    umma_ts(tmem_base + 256u + static_cast<uint32_t>(t) * 64u, p_taddr + ks * 8,
-                            smem_desc_at(dv, v_addr + ks * 16 * 128), idesc_pv, (j > 0 || ks > 0) ? 1u : 0u);
-                umma_commit(&o_full[t]);
+                    for (int ks = 0; ks < ATT_BN / 16; ++ks)
+                        umma_ts(tmem_base + 256u + static_cast<uint32_t>(t) * 64u, p_taddr + ks * 8,
+                                make_smem_desc(v_addr + ks * 16 * 128, CHUNK_BYTES, 1024, kSwizzle128), idesc_pv,
+                                (j > 0 || ks > 0) ? 1u : 0u);
+                    umma_commit(&o_full[t]);
+                }
+                __syncwarp();
             };
             mbar_wait(q_full, 0);
             mbar_wait(&kv_full[0], 0);
@@ -182,23 +188,23 @@ flash_attn3_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 // S_t is free as soon as P_t is written: the next QK goes first so the softmax warps get their next
                 // scores one P.V earlier (they only need O again at their rescale point, after the max pass).
                 wait_p(0, j);
-                if (dbg && j < 32) dbg[4 * j] = clock64();
+                if (dbg && leader && j < 32) dbg[4 * j] = clock64();
                 if (more) issue_qk(0, j + 1);
                 issue_pv(0, j);
-                if (dbg && j < 32) dbg[4 * j + 1] = clock64();
+                if (dbg && leader && j < 32) dbg[4 * j + 1] = clock64();
                 if (b_active) {
                     wait_p(1, j);
-                    if (dbg && j < 32) dbg[4 * j + 2] = clock64();
+                    if (dbg && leader && j < 32) dbg[4 * j + 2] = clock64();
                     if (more) issue_qk(1, j + 1);
                     issue_pv(1, j);
-                    if (dbg && j < 32) dbg[4 * j + 3] = clock64();
+                    if (dbg && leader && j < 32) dbg[4 * j + 3] = clock64();
                 }
                 // every MMA that read stage j has been issued; this commit fires when they are all done.
                 // QK(j+1) issued above read stage j+1, which only delays the release slightly.
-                umma_commit(&kv_empty[j % A3_STAGES]);
+                if (leader) umma_commit(&kv_empty[j % A3_STAGES]);
+                __syncwarp();
             }
         }
-        __syncwarp();
     } else {
         // ================= softmax warps: tile t, one thread per query row =================
         const int t = (warp - 2) >> 2;

@@ -282,8 +282,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // (tap, channel chunk) advance by counting: no division in the loop
             int tap = kc_begin / chunks_per_tap;
             int cc = kc_begin - tap * chunks_per_tap;
+            bool vacant = mbar_test_wait(&empty_bar[0], 1);
             for (int kc = kc_begin; kc < kc_end; ++kc) {
-                mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (!vacant) mbar_wait(&empty_bar[stage], phase ^ 1);
+                // look at the next stage's barrier now: its round trip overlaps this stage's loads
+                int nstage = stage + 1;
+                uint32_t nphase = phase;
+                if (nstage == stages) { nstage = 0; nphase ^= 1; }
+                vacant = (kc + 1 < kc_end) && mbar_test_wait(&empty_bar[nstage], nphase ^ 1);
                 uint8_t* sa = smem + stage * STAGE_BYTES;
                 uint8_t* sb = sa + A_BYTES;
                 mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
@@ -308,7 +314,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     }
                 }
                 tma_load_2d(sb, &tmB, &full_bar[stage], kc * BK, n0);
-                if (++stage == stages) { stage = 0; phase ^= 1; }
+                stage = nstage;
+                phase = nphase;
                 if (++cc == chunks_per_tap) { cc = 0; ++tap; }
             }
         }
@@ -321,12 +328,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t smem_base = smem_u32(smem);
             int stage = 0;
             uint32_t phase = 0;
+            bool ready = mbar_test_wait(&full_bar[0], 0);
             for (int kc = kc_begin; kc < kc_end; ++kc) {
-                mbar_wait(&full_bar[stage], phase);
+                if (!ready) mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
                 if (dbg && kc == kc_begin) dbg[1] = clock64() - t_start;   // first operands landed
                 const uint32_t sa = smem_base + stage * STAGE_BYTES;
                 const uint32_t sb = sa + A_BYTES;
+                // look at the next stage's barrier now: its round trip overlaps the issue of this stage's MMAs
+                int nstage = stage + 1;
+                uint32_t nphase = phase;
+                if (nstage == stages) { nstage = 0; nphase ^= 1; }
+                ready = (kc + 1 < kc_end) && mbar_test_wait(&full_bar[nstage], nphase);
 #pragma unroll
                 for (int k = 0; k < BK / UK; ++k) {
                     const uint64_t bdesc = smem_desc_at(desc0, sb + k * UK * 2);
@@ -337,7 +350,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     }
                 }
                 umma_commit(&empty_bar[stage]);   // frees this smem stage once the MMAs have read it
-                if (++stage == stages) { stage = 0; phase ^= 1; }
+                stage = nstage;
+                phase = nphase;
             }
             umma_commit(acc_bar);                 // accumulator complete
             if (dbg) dbg[2] = clock64() - t_start;                     // all MMAs issued
@@ -429,10 +443,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 fence_proxy_async();
                 asm volatile("bar.sync %0, 128;\n" ::"r"(2 + hf) : "memory");   // the four warps of this chunk parity
-                if (q == 0 && lane == 0) {
-                    if (p.conv) tma_store_4d(&p.omap, box, n_base, w0, h0, i0);
-                    else tma_store_2d(&p.omap, box, n_base, m0);
-                    tma_store_commit();
+                if (q == 0) {
+                    if (elect_one()) {
+                        if (p.conv) tma_store_4d(&p.omap, box, n_base, w0, h0, i0);
+                        else tma_store_2d(&p.omap, box, n_base, m0);
+                        tma_store_commit();
+                    }
+                    __syncwarp();
                 }
                 continue;
             }
@@ -454,7 +471,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
         }   // sub-tiles
-        if (p.tma_store && q == 0 && lane == 0) tma_store_wait_read();   // boxes must outlive the bulk reads
+        if (p.tma_store && q == 0) {
+            if (elect_one()) tma_store_wait_read();   // boxes must outlive the bulk reads (same lane: elect.sync with the
+            __syncwarp();                             // full mask always names the same leader)
+        }
     }
 
     if (dbg && threadIdx.x == 64) dbg[4] = clock64() - t_start;       // epilogue done

@@ -40,14 +40,14 @@ __global__ void __launch_bounds__(128) k(const __grid_constant__ CUtensorMap tmA
     tc_fence_after();
     const uint32_t tmem_base = slot;
     const long long t0 = clock64();
-    if (warp == 0 && (mode == 6 || mode == 7)) {
+    if (warp == 0 && mode >= 6) {
         if (elect_one()) {
             int stage = 0; uint32_t phase = 0;
             for (int kc = 0; kc < ksteps; ++kc) {
-                mbar_wait(&empty[stage], phase ^ 1);
-                mbar_expect_tx(&full[stage], STAGE);
+                if (mode < 8) mbar_wait(&empty[stage], phase ^ 1);
+                mbar_expect_tx(&full[stage], mode == 9 ? 16384 : STAGE);
                 tma_load_2d(smem + stage * STAGE, &tmA, &full[stage], kc * 64, blockIdx.x * 128);
-                tma_load_2d(smem + stage * STAGE + 16384, &tmB, &full[stage], kc * 64, 0);
+                if (mode != 9) tma_load_2d(smem + stage * STAGE + 16384, &tmB, &full[stage], kc * 64, 0);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
         }
@@ -71,7 +71,15 @@ __global__ void __launch_bounds__(128) k(const __grid_constant__ CUtensorMap tmA
         const uint64_t d0 = make_smem_desc(0, 16, 1024, kSwizzle128);
         const uint32_t base = smem_u32(smem);
         int stage = 0; uint32_t phase = 0;
-        if (mode >= 6) {
+        if (mode >= 8) {
+            // producer-rate probe: nobody recycles stages; wait for the LAST load only (the ring is overwritten freely)
+            if (leader) {
+                const int last = (ksteps - 1) % stages;
+                mbar_wait(&full[last], ((ksteps - 1) / stages) & 1);
+            }
+            __syncwarp();
+            ksteps = 0;
+        } else if (mode >= 6) {
             if (leader) {
                 for (int kc = 0; kc < ksteps; ++kc) {
                     mbar_wait(&full[stage], phase);
@@ -158,7 +166,7 @@ void run(int nctas, int stages, int K, long long* out, __half* A, __half* B) {
         long long mx = 0;
         for (int i = 0; i < nctas; ++i) mx = out[i] > mx ? out[i] : mx;
         printf("BN=%3d ctas=%3d stages=%2d K=%5d %-12s %7.1f cycles per K step (slowest CTA)\n", BN, nctas, stages, K,
-               mode == 0 ? "MMA+commit" : mode == 1 ? "TMA only" : mode == 2 ? "full loop" : mode == 3 ? "leader-loop MMA+commit" : mode == 4 ? "leader-loop MMA" : mode == 5 ? "leader-loop fixed-stage" : mode == 6 ? "elected-lane full loop" : "elected-lane TMA only", (double)mx / ksteps);
+               mode == 0 ? "MMA+commit" : mode == 1 ? "TMA only" : mode == 2 ? "full loop" : mode == 3 ? "leader-loop MMA+commit" : mode == 4 ? "leader-loop MMA" : mode == 5 ? "leader-loop fixed-stage" : mode == 6 ? "elected-lane full loop" : mode == 7 ? "elected-lane TMA only" : mode == 8 ? "producer free-running, 2 loads" : "producer free-running, A only", (double)mx / ksteps);
 
     }
 }
