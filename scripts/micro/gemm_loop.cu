@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(128) k(const __grid_constant__ CUtensorMap tmA
     __shared__ uint32_t slot;
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], mode >= 10 ? 2 : 1); mbar_init(&empty[s], 1); }
         mbar_init(done, 1);
         fence_barrier_init();
     }
@@ -40,7 +40,24 @@ __global__ void __launch_bounds__(128) k(const __grid_constant__ CUtensorMap tmA
     tc_fence_after();
     const uint32_t tmem_base = slot;
     const long long t0 = clock64();
-    if (warp == 0 && mode >= 6) {
+    if ((warp == 0 || warp == 2) && mode >= 10) {
+        // two producer lanes: warp 0 loads A, warp 2 loads B (each arrives once on the stage's full barrier)
+        if (elect_one()) {
+            int stage = 0; uint32_t phase = 0;
+            for (int kc = 0; kc < ksteps; ++kc) {
+                mbar_wait(&empty[stage], phase ^ 1);
+                if (warp == 0) {
+                    mbar_expect_tx(&full[stage], 16384);
+                    tma_load_2d(smem + stage * STAGE, &tmA, &full[stage], kc * 64, blockIdx.x * 128);
+                } else {
+                    mbar_expect_tx(&full[stage], BN * 128);
+                    tma_load_2d(smem + stage * STAGE + 16384, &tmB, &full[stage], kc * 64, 0);
+                }
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 0 && mode >= 6) {
         if (elect_one()) {
             int stage = 0; uint32_t phase = 0;
             for (int kc = 0; kc < ksteps; ++kc) {
@@ -71,7 +88,7 @@ __global__ void __launch_bounds__(128) k(const __grid_constant__ CUtensorMap tmA
         const uint64_t d0 = make_smem_desc(0, 16, 1024, kSwizzle128);
         const uint32_t base = smem_u32(smem);
         int stage = 0; uint32_t phase = 0;
-        if (mode >= 8) {
+        if (mode == 8 || mode == 9) {
             // producer-rate probe: nobody recycles stages; wait for the LAST load only (the ring is overwritten freely)
             if (leader) {
                 const int last = (ksteps - 1) % stages;
@@ -85,7 +102,7 @@ __global__ void __launch_bounds__(128) k(const __grid_constant__ CUtensorMap tmA
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = base + stage * STAGE, sb = sa + 16384;
-                    if (mode == 6) {
+                    if (mode == 6 || mode == 10) {
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
                             umma_ss(tmem_base, smem_desc_at(d0, sa + ks * 32), smem_desc_at(d0, sb + ks * 32), idesc, 1u);
@@ -159,14 +176,15 @@ void run(int nctas, int stages, int K, long long* out, __half* A, __half* B) {
     CUtensorMap tA = make_map(A, M, K, 128), tB = make_map(B, BN, K, BN);
     const int smem = stages * (16384 + BN * 128) + (2 * stages + 1) * 8 + 1024;
     cudaFuncSetAttribute(k<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    for (int mode = 0; mode < 8; ++mode) {
+    for (int mode = 6; mode < 12; ++mode) {
+        if (mode == 8 || mode == 9) continue;
         for (int rep = 0; rep < 2; ++rep) k<BN><<<nctas, 128, smem>>>(tA, tB, stages, ksteps, mode, out);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); exit(1); }
         long long mx = 0;
         for (int i = 0; i < nctas; ++i) mx = out[i] > mx ? out[i] : mx;
         printf("BN=%3d ctas=%3d stages=%2d K=%5d %-12s %7.1f cycles per K step (slowest CTA)\n", BN, nctas, stages, K,
-               mode == 0 ? "MMA+commit" : mode == 1 ? "TMA only" : mode == 2 ? "full loop" : mode == 3 ? "leader-loop MMA+commit" : mode == 4 ? "leader-loop MMA" : mode == 5 ? "leader-loop fixed-stage" : mode == 6 ? "elected-lane full loop" : mode == 7 ? "elected-lane TMA only" : mode == 8 ? "producer free-running, 2 loads" : "producer free-running, A only", (double)mx / ksteps);
+               mode == 0 ? "MMA+commit" : mode == 1 ? "TMA only" : mode == 2 ? "full loop" : mode == 3 ? "leader-loop MMA+commit" : mode == 4 ? "leader-loop MMA" : mode == 5 ? "leader-loop fixed-stage" : mode == 6 ? "elected-lane full loop" : mode == 7 ? "elected-lane TMA only" : mode == 10 ? "two producers, full loop" : "two producers, TMA only", (double)mx / ksteps);
 
     }
 }
