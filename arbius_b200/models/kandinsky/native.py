@@ -607,6 +607,6 @@ class NativeMoVQDecoder:
             for blk in blocks:
                 h = blk(h, zq)
             if upc is not None:
-                h = ops.conv3x3(ops.upsample_nearest2x(h), *upc)
+                h = ops.conv3x3(h, *upc, upsample=True)   # nearest 2x folded into the conv
         h = self.norm_out(h, zq, "silu")
         return ops.conv_direct(h, *self.conv_out)

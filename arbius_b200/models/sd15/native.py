@@ -203,7 +203,7 @@ class NativeUNet:
                 if blk["att"] is not None:
                     h = blk["att"][j](h, next(it))
             if blk["up"] is not None:
-                h = ops.conv3x3(ops.upsample_nearest2x(h), blk["up"][0], blk["up"][1])
+                h = ops.conv3x3(h, blk["up"][0], blk["up"][1], upsample=True)   # nearest 2x folded into the conv
         h = ops.groupnorm(h, self.no_w, self.no_b, self.cfg.norm_groups, self.cfg.norm_eps, "silu")
         return ops.conv_direct(h, self.conv_out_w, self.conv_out_b)
 
@@ -311,6 +311,6 @@ class NativeVaeDecoder:
             for r in blk["res"]:
                 h = r(h, None)
             if blk["up"] is not None:
-                h = ops.conv3x3(ops.upsample_nearest2x(h), blk["up"][0], blk["up"][1])
+                h = ops.conv3x3(h, blk["up"][0], blk["up"][1], upsample=True)   # nearest 2x folded into the conv
         h = ops.groupnorm(h, self.no_w, self.no_b, self.cfg.norm_groups, 1e-6, "silu")
         return ops.conv_direct(h, self.co_w, self.co_b)

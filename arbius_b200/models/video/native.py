@@ -278,7 +278,7 @@ class NativeUNet3D:
                     h = blk["tatt"][j](blk["att"][j](h, next(it)))
             if blk["up"] is not None:
                 bb, ff, h2, w2, c = h.shape
-                y = ops.conv3x3(ops.upsample_nearest2x(h.view(bb * ff, h2, w2, c)), blk["up"][0], blk["up"][1])
+                y = ops.conv3x3(h.view(bb * ff, h2, w2, c), blk["up"][0], blk["up"][1], upsample=True)   # nearest 2x folded into the conv
                 h = y.view(bb, ff, 2 * h2, 2 * w2, -1)
         bb, ff, h2, w2, c = h.shape
         y = ops.groupnorm(h.view(bb * ff, h2 * w2, c), self.no_w, self.no_b, self.cfg.norm_groups, self.cfg.norm_eps, "silu")

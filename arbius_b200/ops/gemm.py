@@ -193,8 +193,11 @@ def gemm(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
 def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
             x2: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
             rowbias: Optional[torch.Tensor] = None, act: Optional[str] = None, out_scale: float = 1.0,
-            splitk: int = 0, block_n: int = 0, halo: bool = False, sync=None) -> torch.Tensor:
+            splitk: int = 0, block_n: int = 0, halo: bool = False, sync=None, upsample: bool = False) -> torch.Tensor:
     """3x3 / pad 1 / stride 1 implicit-GEMM conv. x [B,H,W,C1] (+ x2 [B,H,W,C2]), w_packed [Cout, 9*(C1+C2)].
+    ``upsample``: the conv of the nearest-2x upsampled x, [B,2H,2W,Cout], without materialising the upsampled image: a
+    tile holds one parity class of the output, so every tap is a plain TMA box of x (same bytes as conv3x3 of
+    ``upsample_nearest2x(x)``).
     ``sync``: (tick_ptr, site_ptr, mask, top_mask) — the kernel's TMA producer waits for those ranks' flags before its first load
     (the neighbours push their edge rows straight into this buffer's halo rows; parallel/patch.py).
     ``halo``: x (and x2) are [B, H + 2, W, C] — a row band of the image with the neighbouring bands' edge rows (or zeros
@@ -208,12 +211,15 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     c2 = x2.shape[-1] if x2 is not None else 0
     n = w_packed.shape[0]
     assert w_packed.shape[1] == 9 * (c1 + c2)
-    out = torch.empty((b, h, wd, n), dtype=x.dtype, device=x.device)
+    up = 2 if upsample else 1
+    assert not (upsample and (halo or x2 is not None or sync is not None))
+    out = torch.empty((b, up * h, up * wd, n), dtype=x.dtype, device=x.device)
     a = GemmArgs()
     a.a, a.a2, a.w, a.out = x.data_ptr(), native.ptr(x2), w_packed.data_ptr(), out.data_ptr()
     a.bias, a.rowbias, a.residual = native.ptr(bias), native.ptr(rowbias), native.ptr(residual)
-    a.M, a.N, a.K1, a.K2 = b * h * wd, n, c1, c2
+    a.M, a.N, a.K1, a.K2 = up * up * b * h * wd, n, c1, c2
     a.conv, a.nimg, a.H, a.W = 1, b, h, wd
+    a.resample = 2 if upsample else 0
     a.halo = 1 if halo else 0
     if sync is not None:
         a.sync_tick, a.sync_wait, a.sync_wait_mask, a.sync_top_mask = sync
@@ -222,10 +228,11 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
     a.block_n = block_n
     a.ldrb = rowbias.stride(0) if rowbias is not None and rowbias.dim() == 2 else 0
     kc = 9 * (c1 + c2) // 64
-    key = f"conv:{b}x{_canon(h)}x{wd}:{n}:{c1 + c2}" if halo else f"conv:{_canon(b)}x{h}x{wd}:{n}:{c1 + c2}"
+    # (the table is keyed by the OUTPUT image: the fused upsample takes the tile / split-K of the conv it replaces)
+    key = f"conv:{b}x{_canon(h)}x{wd}:{n}:{c1 + c2}" if halo else f"conv:{_canon(b)}x{up * h}x{up * wd}:{n}:{c1 + c2}"
     if RECORD is not None:
         RECORD.append(key)
-    cfg = _tuned_pair(key, f"conv:{b}x{h}x{wd}:{n}:{c1 + c2}") if (splitk == 0 and block_n == 0) else None
+    cfg = _tuned_pair(key, f"conv:{b}x{up * h}x{up * wd}:{n}:{c1 + c2}") if (splitk == 0 and block_n == 0) else None
     if cfg is not None:
         a.block_n, a.splitk = cfg[0], cfg[1]
     else:
@@ -237,8 +244,48 @@ def conv3x3(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor
 
 
 def conv3x3_strided(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
+                    stride: int = 2, pad_mode: int = 0, act: Optional[str] = None, splitk: int = 0,
+                    block_n: int = 0) -> torch.Tensor:
+    """3x3 / stride 2 conv as an implicit GEMM whose TMA boxes step two pixels per element along W and H (no gathered
+    copy of the input). pad_mode 0: pad 1 all round; 1: pad right / bottom only (the VAE encoder's).
+    The split-K and the K order are those of the gathered form (``conv3x3_strided_gather``), so the bytes are too."""
+    if stride != 2 or x.shape[-1] % 64:
+        return conv3x3_strided_gather(x, w_packed, bias, stride=stride, pad_mode=pad_mode, act=act)
+    lib = native.load()
+    b, h, wd, c = x.shape
+    ho = (h + (2 if pad_mode == 0 else 1) - 3) // 2 + 1
+    wo = (wd + (2 if pad_mode == 0 else 1) - 3) // 2 + 1
+    n = w_packed.shape[0]
+    assert x.is_contiguous() and w_packed.is_contiguous() and w_packed.shape[1] == 9 * c
+    out = torch.empty((b, ho, wo, n), dtype=x.dtype, device=x.device)
+    a = GemmArgs()
+    a.a, a.w, a.out, a.bias = x.data_ptr(), w_packed.data_ptr(), out.data_ptr(), native.ptr(bias)
+    a.M, a.N, a.K1, a.K2 = b * ho * wo, n, c, 0
+    a.conv, a.nimg, a.H, a.W = 1, b, ho, wo
+    a.resample, a.pad_lo, a.Hin, a.Win = 1, (1 if pad_mode == 0 else 0), h, wd
+    a.act, a.geglu, a.out_scale = ACT[act], 0, 1.0
+    a.dtype = native.dtype_code(x.dtype)
+    a.block_n = block_n
+    # the gathered form ran as a linear GEMM [M, 9C] x [9C, N]: same table key, so the same split-K
+    m = a.M
+    key = f"lin:{_canon(m)}:{n}:{9 * c}"
+    if RECORD is not None:
+        RECORD.append(key)
+    cfg = _tuned_pair(key, f"lin:{m}:{n}:{9 * c}") if (splitk == 0 and block_n == 0) else None
+    if cfg is not None:
+        a.block_n, a.splitk = cfg[0], cfg[1]
+    else:
+        a.splitk = splitk if splitk > 0 else auto_splitk(_canon(m), n, 9 * c // 64)
+    if a.splitk > 1:
+        a.workspace = _workspace(a.splitk * m * n * 4, x.device).data_ptr()
+    native.check(lib.ab_gemm(C.byref(a), native.stream_ptr()), "ab_gemm(conv, stride 2)")
+    return out
+
+
+def conv3x3_strided_gather(x: torch.Tensor, w_packed: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
                     stride: int = 2, pad_mode: int = 0, act: Optional[str] = None) -> torch.Tensor:
-    """Strided 3x3 conv = gather (ab_im2col3x3) + tcgen05 GEMM. pad_mode 0: pad 1 all round; 1: right/bottom."""
+    """Strided 3x3 conv = gather (ab_im2col3x3) + tcgen05 GEMM. pad_mode 0: pad 1 all round; 1: right/bottom.
+    The fallback of ``conv3x3_strided`` (channel counts that are not multiples of 64) and its test oracle."""
     lib = native.load()
     b, h, wd, c = x.shape
     ho = (h + (2 if pad_mode == 0 else 1) - 3) // stride + 1

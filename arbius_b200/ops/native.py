@@ -42,6 +42,7 @@ class GemmArgs(C.Structure):
         ("ldrb", C.c_int),
         ("halo", C.c_int),
         ("sync_tick", C.c_void_p), ("sync_wait", C.c_void_p), ("sync_wait_mask", C.c_uint), ("sync_top_mask", C.c_uint),
+        ("resample", C.c_int), ("pad_lo", C.c_int), ("Hin", C.c_int), ("Win", C.c_int),
     ]
 
 

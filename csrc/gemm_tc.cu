@@ -69,6 +69,9 @@ struct GemmParams {
     const unsigned int* sync_wait;
     unsigned int sync_wait_mask;
     unsigned int sync_top_mask;   // the ranks (of sync_wait_mask) whose rows fill the TOP halo row; the others fill the bottom
+    // resampling folded into the conv's coordinates (ab_gemm_args.resample): 1 = stride 2 (H, W = output size, the A
+    // map has traversal stride 2 along W and H), 2 = nearest 2x upsample (H, W = input size, one tile = one parity class)
+    int resample, pad_lo;
     alignas(64) CUtensorMap amaps[8];
     alignas(64) CUtensorMap omap;
 };
@@ -208,12 +211,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ---- tile coordinates -------------------------------------------------------------------
     const int n0 = blockIdx.y * BN;
     // sub-tile s of this CTA is M tile blockIdx.x * MT + s
-    int tile_ms[MT], i0s[MT], h0s[MT], w0s[MT], m0s[MT];
+    int tile_ms[MT], i0s[MT], h0s[MT], w0s[MT], m0s[MT], pys[MT], pxs[MT];
 #pragma unroll
     for (int s = 0; s < MT; ++s) {
-        const int tm = blockIdx.x * MT + s;
+        int tm = blockIdx.x * MT + s;
         tile_ms[s] = tm;
-        i0s[s] = h0s[s] = w0s[s] = m0s[s] = 0;
+        i0s[s] = h0s[s] = w0s[s] = m0s[s] = pys[s] = pxs[s] = 0;
+        if (p.resample == 2) {            // four parity classes per low-resolution tile
+            pys[s] = (tm >> 1) & 1;
+            pxs[s] = tm & 1;
+            tm >>= 2;
+        }
         if (p.conv) {
             const int tw = tm % p.tiles_w;
             const int th = (tm / p.tiles_w) % p.tiles_h;
@@ -303,7 +311,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         // conv == 1: 3x3 taps; conv == 2: 3x1 taps along H only (temporal Conv3d (3,1,1) on [B, F, HW, C])
                         const int dh = p.conv == 2 ? tap - 1 : tap / 3 - 1;
                         const int dw = p.conv == 2 ? 0 : tap % 3 - 1;
-                        tma_load_4d(sas, ma, &full_bar[stage], c0, w0s[s] + dw, h0s[s] + dh + p.halo, i0s[s]);
+                        if (p.resample == 0) {
+                            tma_load_4d(sas, ma, &full_bar[stage], c0, w0s[s] + dw, h0s[s] + dh + p.halo, i0s[s]);
+                        } else if (p.resample == 1) {
+                            // stride 2: the map steps two pixels per element along W and H
+                            tma_load_4d(sas, ma, &full_bar[stage], c0, 2 * w0s[s] + dw + 1 - p.pad_lo,
+                                        2 * h0s[s] + dh + 1 - p.pad_lo, i0s[s]);
+                        } else {
+                            // nearest 2x upsample: upsampled pixel 2y + py + dh is low-resolution pixel y + ((py + dh) >> 1)
+                            tma_load_4d(sas, ma, &full_bar[stage], c0, w0s[s] + ((pxs[s] + dw) >> 1),
+                                        h0s[s] + ((pys[s] + dh) >> 1), i0s[s]);
+                        }
                     } else {
                         if (p.nsrc > 1) {
                             const int src = tile_ms[s] / p.tiles_per_src;
@@ -408,6 +426,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int ww = w0 + wl, hh = h0 + hl, ii = i0 + il;
             row_ok = (ww < p.W) && (hh < p.H) && (ii < p.nimg);
             out_row = (static_cast<long long>(ii) * p.H + hh) * p.W + ww;
+            if (p.resample == 2)   // this tile's parity class of the [nimg, 2H, 2W] output
+                out_row = (static_cast<long long>(ii) * (2 * p.H) + 2 * hh + pys[s]) * (2 * p.W) + 2 * ww + pxs[s];
             grp = ii;
         } else {
             out_row = m0 + r;
@@ -540,11 +560,22 @@ static EncodeTiledFn get_encode_fn() {
 }  // namespace ab
 
 // Exposed for the other translation units (attention uses the same encoder).
+extern "C" int ab_make_tensor_map_strided(CUtensorMap* out, int dtype, int rank, const void* base, const uint64_t* dims,
+                                          const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes,
+                                          const uint32_t* elem_strides);
 extern "C" int ab_make_tensor_map(CUtensorMap* out, int dtype, int rank, const void* base, const uint64_t* dims,
                                   const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes) {
+    return ab_make_tensor_map_strided(out, dtype, rank, base, dims, strides_bytes, box, swizzle_bytes, nullptr);
+}
+// elem_strides (or NULL = all 1): traversal stride per dimension; a box of `box[i]` tensor elements then delivers
+// ceil(box[i] / elem_strides[i]) of them (the strided conv reads every second pixel this way).
+extern "C" int ab_make_tensor_map_strided(CUtensorMap* out, int dtype, int rank, const void* base, const uint64_t* dims,
+                                          const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes,
+                                          const uint32_t* elem_strides) {
     auto fn = ab::get_encode_fn();
     if (!fn) { ab_set_error("cuTensorMapEncodeTiled entry point not available"); return -1; }
     cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    if (elem_strides) for (int i = 0; i < rank && i < 5; ++i) estr[i] = elem_strides[i];
     CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                           : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
                           : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
@@ -703,7 +734,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     AB_REQUIRE(Ktot % 8 == 0, "K must be a multiple of 8 (16-byte rows for TMA)");
     if (a->K2 > 0) AB_REQUIRE(a->K1 % BK == 0 && a->a2, "virtual concat needs K1 % 64 == 0 and a2");
     if (a->conv) AB_REQUIRE(a->K1 % BK == 0 && a->K2 % BK == 0, "conv needs channel counts that are multiples of 64");
-    if (a->conv) AB_REQUIRE(a->M == a->nimg * a->H * a->W, "conv: M != nimg*H*W");
+    if (a->conv) AB_REQUIRE(a->M == (a->resample == 2 ? 4 : 1) * a->nimg * a->H * a->W, "conv: M != nimg*H*W (x4 with the 2x upsample)");
     if (a->geglu) AB_REQUIRE(a->N % 32 == 0, "geglu needs N % 32 == 0");
 
     GemmParams p{};
@@ -718,6 +749,15 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     p.k1_chunks = (a->K2 > 0 || a->conv) ? a->K1 / BK : (a->K1 + BK - 1) / BK;
     p.k2_chunks = a->K2 > 0 ? (a->conv ? a->K2 / BK : (a->K2 + BK - 1) / BK) : 0;
     p.conv = a->conv; p.nimg = a->nimg; p.H = a->H; p.W = a->W; p.halo = a->halo;
+    p.resample = a->resample; p.pad_lo = a->pad_lo;
+    AB_REQUIRE(a->resample >= 0 && a->resample <= 2, "resample: 0, 1 (stride 2) or 2 (nearest 2x upsample)");
+    if (a->resample) {
+        AB_REQUIRE(a->conv == 1 && a->halo == 0 && a->K2 == 0 && !a->sync_wait && !d, "resample: plain 3x3 conv only");
+        AB_REQUIRE(a->pad_lo == 0 || a->pad_lo == 1, "pad_lo is 0 or 1");
+        if (a->resample == 1)
+            AB_REQUIRE(a->Hin > 0 && a->Win > 0 && 2 * (a->H - 1) + 2 - a->pad_lo < a->Hin + 2 &&
+                       2 * (a->W - 1) + 2 - a->pad_lo < a->Win + 2, "stride 2: input size does not match the output size");
+    }
     AB_REQUIRE(a->halo == 0 || (a->halo == 1 && a->conv != 0), "halo rows (0 or 1) exist in the conv modes only");
     p.rows_per_group = a->conv ? a->H * a->W : a->rows_per_group;
     p.act = a->act; p.geglu = a->geglu;
@@ -735,6 +775,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         p.tiles_w = (a->W + ct.bw - 1) / ct.bw;
         p.tiles_h = (a->H + ct.bh - 1) / ct.bh;
         tiles_m = p.tiles_w * p.tiles_h * ((a->nimg + ct.bi - 1) / ct.bi);
+        if (a->resample == 2) tiles_m *= 4;   // one tile per parity class of each low-resolution box
     } else {
         tiles_m = (a->M + BM - 1) / BM;
     }
@@ -790,7 +831,14 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
         uint64_t dims[4] = {(uint64_t)a->K1, (uint64_t)a->W, Hin, (uint64_t)a->nimg};
         uint64_t str[3] = {(uint64_t)a->K1 * esz, (uint64_t)a->W * a->K1 * esz, Hin * a->W * a->K1 * esz};
         uint32_t box[4] = {BK, (uint32_t)ct.bw, (uint32_t)ct.bh, (uint32_t)ct.bi};
-        if (ab_make_tensor_map(&tmA, a->dtype, 4, a->a, dims, str, box, 128)) return -1;
+        if (a->resample == 1) {
+            // stride 2: the map is over the INPUT image and steps two pixels per delivered element along W and H
+            uint64_t dims_s[4] = {(uint64_t)a->K1, (uint64_t)a->Win, (uint64_t)a->Hin, (uint64_t)a->nimg};
+            uint64_t str_s[3] = {(uint64_t)a->K1 * esz, (uint64_t)a->Win * a->K1 * esz, (uint64_t)a->Hin * a->Win * a->K1 * esz};
+            uint32_t box_s[4] = {BK, 2u * ct.bw, 2u * ct.bh, (uint32_t)ct.bi};
+            uint32_t es[4] = {1, 2, 2, 1};
+            if (ab_make_tensor_map_strided(&tmA, a->dtype, 4, a->a, dims_s, str_s, box_s, 128, es)) return -1;
+        } else if (ab_make_tensor_map(&tmA, a->dtype, 4, a->a, dims, str, box, 128)) return -1;
         tmA2 = tmA;
         if (a->K2 > 0) {
             uint64_t dims2[4] = {(uint64_t)a->K2, (uint64_t)a->W, Hin, (uint64_t)a->nimg};
@@ -820,7 +868,7 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
 
     static const bool tma_store_on = [] { const char* e = getenv("AB_TMA_STORE"); return !(e && e[0] == '0'); }();
     p.tma_store = 0;
-    if (tma_store_on && !a->geglu && splitk <= 1 && !rs && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0) {
+    if (tma_store_on && !a->geglu && splitk <= 1 && !rs && a->resample != 2 && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0) {
         const uint64_t ld = (uint64_t)p.ldo * esz;
         if (a->conv) {
             uint64_t dims[4] = {(uint64_t)a->N, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};

@@ -75,6 +75,16 @@ typedef struct {
   const unsigned int* sync_tick; const unsigned int* sync_wait; unsigned int sync_wait_mask;
   unsigned int sync_top_mask;   /* conv + halo: the ranks of sync_wait_mask that fill the TOP halo row (the rest fill the
                                  * bottom one); only tiles that touch a halo row wait, and only for that neighbour */
+  /* conv == 1 only: resampling folded into the conv's TMA coordinates (no gathered or upsampled copy of the input).
+   *   0  none (3x3, stride 1, pad 1)
+   *   1  stride 2: H, W are the OUTPUT size, A is [nimg, Hin, Win, K]; tap (dy, dx) of output (y, x) reads input
+   *      (2y + dy - pad_lo, 2x + dx - pad_lo) through a tensor map whose W and H traversal strides are 2.
+   *      pad_lo = 1: pad 1 all round (Hin = 2H or 2H - 1); pad_lo = 0: pad right / bottom only (Hin = 2H + 1 ... ).
+   *   2  nearest 2x upsample before the conv: H, W are the INPUT size, the output is [nimg, 2H, 2W, N]. A tile holds the
+   *      outputs of one parity class (Y = 2y + py, X = 2x + px) of a low-resolution box, so that every tap reads a plain
+   *      box of the low-resolution input at offset ((py + dy - 1) >> 1, (px + dx - 1) >> 1).
+   * Both give the bytes of the unfused op (same taps, same K order, same split-K). Not combined with halo / a2 / sync. */
+  int resample; int pad_lo; int Hin; int Win;
 } ab_gemm_args;
 int ab_gemm(const ab_gemm_args* args, void* stream);
 /* Multi-GPU forms of the same kernel (one NVSwitch box; pointers may be peer-mapped addresses).

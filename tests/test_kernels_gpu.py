@@ -146,6 +146,47 @@ def test_conv_strided_and_direct(dt):
 
 
 @pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("b,h,w,cin,cout,kw", [(2, 32, 32, 640, 640, {}), (2, 8, 8, 1280, 1280, {}), (1, 12, 20, 64, 128, {}),
+                                                (3, 5, 9, 128, 64, {}), (2, 16, 16, 1280, 1280, dict(splitk=3, block_n=128)),
+                                                (1, 64, 64, 256, 256, dict(block_n=256)), (1, 128, 128, 128, 128, {})])
+def test_conv3x3_with_folded_upsample_equals_the_unfused_bytes(dt, b, h, w, cin, cout, kw):
+    """K11: the nearest-2x upsample lives in the conv's TMA coordinates (one tile = one parity class of the output)."""
+    from arbius_b200 import ops
+    x = torch.randn(b, h, w, cin, device="cuda", dtype=dt)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda", dtype=dt) / (9 * cin) ** 0.5
+    bias = torch.randn(cout, device="cuda", dtype=dt)
+    wp = ops.pack_conv_weight(wt)
+    fused = ops.conv3x3(x, wp, bias, upsample=True, **kw)
+    plain = ops.conv3x3(ops.upsample_nearest2x(x), wp, bias, **kw)
+    assert fused.shape == (b, 2 * h, 2 * w, cout)
+    assert torch.equal(fused, plain)
+    up = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest")
+    ref = F.conv2d(up, wt.float(), bias.float(), padding=1).permute(0, 2, 3, 1)
+    _close(fused, ref, dt)
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("b,h,w,cin,cout,pad_mode", [(2, 64, 64, 320, 320, 0), (2, 16, 16, 1280, 1280, 0), (1, 33, 47, 64, 128, 0),
+                                                      (1, 64, 64, 128, 128, 1), (2, 30, 22, 128, 64, 1), (1, 512, 512, 128, 128, 1)])
+def test_conv3x3_stride2_through_tma_strides_equals_the_gathered_bytes(dt, b, h, w, cin, cout, pad_mode):
+    """K11: stride 2 is the traversal stride of the A tensor map (no im2col copy); both paddings of the models."""
+    from arbius_b200 import ops
+    x = torch.randn(b, h, w, cin, device="cuda", dtype=dt)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda", dtype=dt) / (9 * cin) ** 0.5
+    bias = torch.randn(cout, device="cuda", dtype=dt)
+    wp = ops.pack_conv_weight(wt)
+    fused = ops.conv3x3_strided(x, wp, bias, stride=2, pad_mode=pad_mode)
+    gathered = ops.conv3x3_strided_gather(x, wp, bias, stride=2, pad_mode=pad_mode)
+    assert fused.shape == gathered.shape
+    assert torch.equal(fused, gathered)
+    xin = x.float().permute(0, 3, 1, 2)
+    if pad_mode == 1:
+        xin = F.pad(xin, (0, 1, 0, 1))
+    ref = F.conv2d(xin, wt.float(), bias.float(), padding=1 if pad_mode == 0 else 0, stride=2).permute(0, 2, 3, 1)
+    _close(fused, ref, dt)
+
+
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("n,hw,c1,c2,act", [(2, 4096, 320, 0, "silu"), (2, 1024, 1280, 640, "silu"),
                                             (2, 64, 1280, 1280, None), (1, 16384, 128, 0, "silu"),
                                             (3, 100, 64, 0, None), (2, 256, 1920, 0, "silu")])
