@@ -72,6 +72,11 @@ struct GemmParams {
     // resampling folded into the conv's coordinates (ab_gemm_args.resample): 1 = stride 2 (H, W = output size, the A
     // map has traversal stride 2 along W and H), 2 = nearest 2x upsample (H, W = input size, one tile = one parity class)
     int resample, pad_lo;
+    // M-persistent launches: the grid has fewer CTAs along x than there are (groups of MT) M tiles and CTA x walks tiles
+    // x, x + gridDim.x, ... of its N column. Barrier init, TMEM allocation and the launch itself are paid once, and the
+    // producer already loads the next tile's operands while the epilogue drains this tile's accumulator. For short K
+    // loops (a 128-row tile of a K=320 GEMM is five K steps) those fixed costs were most of a CTA's life.
+    int tiles_x;
     alignas(64) CUtensorMap amaps[8];
     alignas(64) CUtensorMap omap;
 };
@@ -200,7 +205,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + stages * STAGE_BYTES);
     uint64_t* empty_bar = full_bar + stages;
     uint64_t* acc_bar = empty_bar + stages;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+    uint64_t* acc_free = acc_bar + 1;             // epilogue -> MMA: the accumulator has been read (persistent launches)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_free + 1);
     float* sbias = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot) + 4 + 15) & ~uintptr_t(15));  // [MT][BN]
 
     const int warp = threadIdx.x >> 5;
@@ -210,11 +216,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     // ---- tile coordinates -------------------------------------------------------------------
     const int n0 = blockIdx.y * BN;
-    // sub-tile s of this CTA is M tile blockIdx.x * MT + s
+    // sub-tile s of tile group tb is M tile tb * MT + s; a CTA starts with group blockIdx.x (and, in a persistent launch,
+    // goes on with blockIdx.x + gridDim.x, ...: every role calls set_tile at the top of each of its iterations)
     int tile_ms[MT], i0s[MT], h0s[MT], w0s[MT], m0s[MT], pys[MT], pxs[MT];
+    auto set_tile = [&](int tb) {
 #pragma unroll
     for (int s = 0; s < MT; ++s) {
-        int tm = blockIdx.x * MT + s;
+        int tm = tb * MT + s;
         tile_ms[s] = tm;
         i0s[s] = h0s[s] = w0s[s] = m0s[s] = pys[s] = pxs[s] = 0;
         if (p.resample == 2) {            // four parity classes per low-resolution tile
@@ -233,6 +241,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             m0s[s] = tm * BM;
         }
     }
+    };
+    set_tile(blockIdx.x);
     const int chunks_per_tap = p.k1_chunks + p.k2_chunks;
     const int total_chunks = p.taps * chunks_per_tap;
     const int kc_begin = blockIdx.z * p.chunks_per_split;
@@ -248,6 +258,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(acc_bar, 1);
+        mbar_init(acc_free, GEMM_THREADS - 64);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -287,17 +298,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             int stage = 0;
             uint32_t phase = 0;
+            bool vacant = mbar_test_wait(&empty_bar[0], 1);
+            for (int tb = blockIdx.x; tb < p.tiles_x; tb += gridDim.x) {
+            set_tile(tb);
             // (tap, channel chunk) advance by counting: no division in the loop
             int tap = kc_begin / chunks_per_tap;
             int cc = kc_begin - tap * chunks_per_tap;
-            bool vacant = mbar_test_wait(&empty_bar[0], 1);
             for (int kc = kc_begin; kc < kc_end; ++kc) {
                 if (!vacant) mbar_wait(&empty_bar[stage], phase ^ 1);
                 // look at the next stage's barrier now: its round trip overlaps this stage's loads
                 int nstage = stage + 1;
                 uint32_t nphase = phase;
                 if (nstage == stages) { nstage = 0; nphase ^= 1; }
-                vacant = (kc + 1 < kc_end) && mbar_test_wait(&empty_bar[nstage], nphase ^ 1);
+                vacant = (kc + 1 < kc_end || tb + gridDim.x < p.tiles_x) && mbar_test_wait(&empty_bar[nstage], nphase ^ 1);
                 uint8_t* sa = smem + stage * STAGE_BYTES;
                 uint8_t* sb = sa + A_BYTES;
                 mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
@@ -336,6 +349,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 phase = nphase;
                 if (++cc == chunks_per_tap) { cc = 0; ++tap; }
             }
+            }   // tiles of this CTA
         }
         __syncwarp();
     } else if (warp == 1) {
@@ -347,17 +361,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             int stage = 0;
             uint32_t phase = 0;
             bool ready = mbar_test_wait(&full_bar[0], 0);
+            int it = 0;
+            for (int tb = blockIdx.x; tb < p.tiles_x; tb += gridDim.x, ++it) {
+            if (it > 0) {                         // the epilogue warps have read the previous tile out of tensor memory
+                mbar_wait(acc_free, (it - 1) & 1);
+                tc_fence_after();
+            }
             for (int kc = kc_begin; kc < kc_end; ++kc) {
                 if (!ready) mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
-                if (dbg && kc == kc_begin) dbg[1] = clock64() - t_start;   // first operands landed
+                if (dbg && kc == kc_begin && it == 0) dbg[1] = clock64() - t_start;   // first operands landed
                 const uint32_t sa = smem_base + stage * STAGE_BYTES;
                 const uint32_t sb = sa + A_BYTES;
                 // look at the next stage's barrier now: its round trip overlaps the issue of this stage's MMAs
                 int nstage = stage + 1;
                 uint32_t nphase = phase;
                 if (nstage == stages) { nstage = 0; nphase ^= 1; }
-                ready = (kc + 1 < kc_end) && mbar_test_wait(&full_bar[nstage], nphase);
+                ready = (kc + 1 < kc_end || tb + gridDim.x < p.tiles_x) && mbar_test_wait(&full_bar[nstage], nphase);
 #pragma unroll
                 for (int k = 0; k < BK / UK; ++k) {
                     const uint64_t bdesc = smem_desc_at(desc0, sb + k * UK * 2);
@@ -372,7 +392,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 phase = nphase;
             }
             umma_commit(acc_bar);                 // accumulator complete
-            if (dbg) dbg[2] = clock64() - t_start;                     // all MMAs issued
+            if (dbg && it == 0) dbg[2] = clock64() - t_start;          // all MMAs issued
+            }   // tiles of this CTA
         }
         __syncwarp();
     } else {
@@ -380,6 +401,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int q = warp & 3;                   // TMEM lane quarter this warp may read
         const int hf = (warp - 2) >> 2;           // which half of the 32-column chunks this warp handles
         const int r = q * 32 + lane;              // row inside the tile
+        int it = 0;
+        for (int tb = blockIdx.x; tb < p.tiles_x; tb += gridDim.x, ++it) {
+        set_tile(tb);
         // While the main loop runs, stage bias (+ row bias if a whole sub-tile shares one group) in smem.
         bool single_group[MT];
         const bool use_sb = p.splitk <= 1;
@@ -392,7 +416,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 tile_grp = m0s[s] / p.rows_per_group;
                 single_group[s] = (last / p.rows_per_group) == tile_grp;
             } else { single_group[s] = true; tile_grp = 0; }
-            if (use_sb) {
+            // (a persistent CTA keeps its N column: without a row bias the staged values do not change between tiles)
+            if (use_sb && (it == 0 || p.rowbias)) {
                 const T* bias = reinterpret_cast<const T*>(p.bias);
                 const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
                 for (int n = threadIdx.x - 64; n < BN; n += GEMM_THREADS - 64) {
@@ -406,10 +431,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             }
         }
-        if (use_sb) asm volatile("bar.sync 1, 256;\n" ::: "memory");
-        mbar_wait(acc_bar, 0);
+        if (use_sb && (it == 0 || p.rowbias)) asm volatile("bar.sync 1, 256;\n" ::: "memory");
+        mbar_wait(acc_bar, it & 1);
         tc_fence_after();
-        if (dbg && threadIdx.x == 64) dbg[3] = clock64() - t_start;   // accumulator ready
+        if (dbg && threadIdx.x == 64 && it == 0) dbg[3] = clock64() - t_start;   // accumulator ready
 #pragma unroll
         for (int s = 0; s < MT; ++s) {
         const int w0 = w0s[s], h0 = h0s[s], i0 = i0s[s], m0 = m0s[s];
@@ -449,6 +474,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (c >= NCHUNK) break;
             if (!PF) tmem_ld32(taddr + c * 32, raw[0]);
             tmem_wait_ld();
+            if (dbg && threadIdx.x == 64 && it == 0 && j == 0 && s == 0) dbg[6] = clock64() - t_start;   // first chunk in registers
             if (PF && j + 1 < MY_MAX && c + 2 < NCHUNK) tmem_ld32(taddr + (c + 2) * 32, raw[PF ? ((j + 1) & 1) : 0]);
             const int n_base = n0 + c * 32;
             if (p.tma_store) {
@@ -461,16 +487,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias_s + c * 32, rowbias_global, box + r * 64,
                                              (r >> 1) & 3);
                 }
-                fence_proxy_async();
-                asm volatile("bar.sync %0, 128;\n" ::"r"(2 + hf) : "memory");   // the four warps of this chunk parity
-                if (q == 0) {
-                    if (elect_one()) {
-                        if (p.conv) tma_store_4d(&p.omap, box, n_base, w0, h0, i0);
-                        else tma_store_2d(&p.omap, box, n_base, m0);
-                        tma_store_commit();
-                    }
-                    __syncwarp();
-                }
+                if (dbg && threadIdx.x == 64 && it == 0 && j == 0 && s == 0) dbg[7] = clock64() - t_start;   // first chunk staged
                 continue;
             }
             if (row_ok && n_base < p.N) {
@@ -489,8 +506,36 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias_s + c * 32, rowbias_global);
                 }
             }
+            if (dbg && threadIdx.x == 64 && it == 0 && j == 0 && s == 0) dbg[7] = clock64() - t_start;   // first chunk stored
+        }
+        if (p.tma_store) {
+            // every chunk has its own box, so the proxy fence and the barrier are paid once per tile, not once per chunk
+            // (they were ~1 us of each chunk's 1.14 us), and one lane issues the tile's stores back to back
+            fence_proxy_async();
+            asm volatile("bar.sync %0, 128;\n" ::"r"(2 + hf) : "memory");   // the four warps of this chunk parity
+            if (q == 0) {
+                if (elect_one()) {
+                    for (int c = hf; c < NCHUNK; c += 2) {
+                        const int n_base = n0 + c * 32;
+                        if (n_base >= p.N) break;
+                        uint8_t* box = stage_base + c * (BM * 64);
+                        if (p.conv) tma_store_4d(&p.omap, box, n_base, w0, h0, i0);
+                        else tma_store_2d(&p.omap, box, n_base, m0);
+                    }
+                    tma_store_commit();
+                }
+                __syncwarp();
+            }
         }
         }   // sub-tiles
+        if (tb + gridDim.x < p.tiles_x) {
+            // persistent launch: hand the accumulator back to the MMA lane (every epilogue thread's tcgen05.ld has
+            // completed: each chunk ends with tcgen05.wait::ld), and keep sbias until everyone has used it
+            tc_fence_before();
+            mbar_arrive(acc_free);
+            if (p.rowbias) asm volatile("bar.sync 1, 256;\n" ::: "memory");   // sbias is rewritten for the next tile
+        }
+        }   // tiles of this CTA
         if (p.tma_store && q == 0) {
             if (elect_one()) tma_store_wait_read();   // boxes must outlive the bulk reads (same lane: elect.sync with the
             __syncwarp();                             // full mask always names the same leader)
@@ -890,7 +935,23 @@ extern "C" int ab_gemm_dist(const ab_gemm_args* a, const ab_gemm_dist_args* d, i
     // 18 K steps got 20 % slower) on problems that still give every SM two waves
     p.mt = (mt_on && !ag && bn == 256 && tiles_m % 2 == 0 && p.chunks_per_split >= 24 &&
             static_cast<long long>(tiles_m / 2) * n_tiles * grid_z >= 2LL * ab_sm_count()) ? 2 : 1;
-    dim3 grid(tiles_m / p.mt, n_tiles, grid_z);
+    p.tiles_x = tiles_m / p.mt;
+    int grid_x = p.tiles_x;
+    {
+        // M-persistent launch for short K loops on grids of several waves (GemmParams.tiles_x): as many CTAs as are
+        // resident at once, each walking the M tiles of its N column. The TMA-store staging boxes live in the pipeline
+        // stages, which a persistent CTA is already refilling, so these launches store from registers.
+        static const int persist_mode = [] { const char* e = getenv("AB_GEMM_PERSIST"); return e ? atoi(e) : 1; }();
+        const int per_sm = (bn <= 160 && p.mt == 1) ? 2 : 1;
+        const long long slots = static_cast<long long>(ab_sm_count()) * per_sm;
+        const int gx = static_cast<int>(slots / n_tiles);
+        if (persist_mode && splitk <= 1 && !rs && !ag && !a->sync_wait && p.chunks_per_split <= 16 && gx >= 1 &&
+            p.tiles_x >= 3 * gx) {
+            grid_x = gx;
+            p.tma_store = 0;
+        }
+    }
+    dim3 grid(grid_x, n_tiles, grid_z);
     int epi = a->geglu ? EPI_GEGLU
             : a->act == ACT_NONE ? EPI_NONE
             : a->act == ACT_SILU ? EPI_SILU

@@ -46,7 +46,8 @@ def run(label, fn, grid_hint=4096):
     mhz = sm_mhz()
     med = lambda t: float(t.median()) / mhz
     print(f"{label:46s} {us:7.1f} us/call  ctas={d.shape[0]:4d}  setup {med(d[:,0]):5.2f}  first-operands {med(d[:,1]-d[:,0]):5.2f}  "
-          f"mainloop-issue {med(d[:,2]-d[:,1]):6.2f}  acc-ready {med(d[:,3]-d[:,2]):5.2f}  epilogue {med(d[:,4]-d[:,3]):5.2f}  "
+          f"mainloop-issue {med(d[:,2]-d[:,1]):6.2f}  acc-ready {med(d[:,3]-d[:,2]):5.2f}  epilogue {med(d[:,4]-d[:,3]):5.2f} "
+          f"(first chunk: tmem-ld {med(d[:,6]-d[:,3]):4.2f} math+store {med(d[:,7]-d[:,6]):4.2f})  "
           f"total {med(d[:,5]):6.2f} us @ {mhz:.0f} MHz", flush=True)
 
 

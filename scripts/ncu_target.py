@@ -11,6 +11,11 @@ if what == "gemm":
         x = torch.randn(m, k, device="cuda", dtype=dt); w = torch.randn(n, k, device="cuda", dtype=dt); b = torch.randn(n, device="cuda", dtype=dt)
         for _ in range(3):
             ops.gemm(x, w, b, block_n=bn, splitk=1)
+elif what == "gemmbig":    # ZeroScope's short-K projections: M = 442368 rows, K = 320 (five K steps per tile), M-persistent launch
+    for (m, n, k, bn) in [(442368, 320, 320, 160)]:
+        x = torch.randn(m, k, device="cuda", dtype=dt); w = torch.randn(n, k, device="cuda", dtype=dt); b = torch.randn(n, device="cuda", dtype=dt)
+        for _ in range(3):
+            ops.gemm(x, w, b, block_n=bn, splitk=1)
 elif what == "conv":
     for (b_, h, w_, ci, co, bn) in [(2, 64, 64, 320, 320, 160), (2, 32, 32, 640, 640, 160), (1, 256, 256, 256, 256, 160)]:
         x = torch.randn(b_, h, w_, ci, device="cuda", dtype=dt); wt = torch.randn(co, 9 * ci, device="cuda", dtype=dt); b = torch.randn(co, device="cuda", dtype=dt)

@@ -72,6 +72,26 @@ def bench_key(key, dt=torch.float16, only_splitk=None):
                     res[(bn, sk)] = time_graph(fn)
                 except RuntimeError as e:
                     res[(bn, sk)] = float("inf")
+    elif kind == "tconv":
+        bfhw, n, c = parts[1], int(parts[2]), int(parts[3])
+        b_, f, hw = (int(v) for v in bfhw.split("x"))
+        wbytes = n * 3 * c * 2
+        ncopy = max(2, min(REPS, (300 << 20) // wbytes))
+        x = torch.randn(b_, f, hw, c, device="cuda", dtype=dt)
+        ws = [torch.randn(n, 3 * c, device="cuda", dtype=dt) / (3 * c) ** 0.5 for _ in range(ncopy)]
+        bias = torch.randn(n, device="cuda", dtype=dt)
+        flops = 2.0 * b_ * f * hw * n * 3 * c
+        for bn in BNS:
+            if bn > 64 and bn >= 2 * n:
+                continue
+            for sk in ([only_splitk] if only_splitk else [1]):
+                def fn():
+                    for i in range(REPS):
+                        ops.conv_temporal(x, ws[i % ncopy], bias, block_n=bn, splitk=sk)
+                try:
+                    res[(bn, sk)] = time_graph(fn)
+                except RuntimeError:
+                    res[(bn, sk)] = float("inf")
     else:
         bhw, n, c = parts[1], int(parts[2]), int(parts[3])
         b_, h, w = (int(v) for v in bhw.split("x"))
@@ -201,9 +221,51 @@ def tune_kandinsky(a):
     print(f"tuned {len(new)} shapes; merged table in gpurun_out/tuned_sm100.json", flush=True)
 
 
+def tune_video(a):
+    """ZeroScope XL's UNet3D shapes (1024x576x24): the best TILE WIDTH for every recorded shape with split-K held at what
+    the heuristic gives today, so the bytes of a task do not change. Writes the merged table."""
+    from arbius_b200.models.video.pipeline import TextToVideoConfig, TextToVideoPipeline
+    pipe = TextToVideoPipeline(TextToVideoConfig.zeroscope_xl(), backend="native", device="cuda", dtype=torch.float16,
+                               family="zeroscopev2xl", use_graph=False)
+    G.RECORD = []
+    pipe.generate("cat", num_inference_steps=1, seed=1)
+    torch.cuda.synchronize()
+    counts = Counter(k for k in G.RECORD if k.split(":")[0] in ("lin", "geglu", "conv", "tconv"))
+    G.RECORD = None
+    del pipe
+    torch.cuda.empty_cache()
+    table = _load_table()
+    new, report = {}, []
+    for key, cnt in sorted(counts.items(), key=lambda kv: -kv[1]):
+        parts = key.split(":")
+        n = int(parts[2])
+        if parts[0] == "conv":
+            b_, h, w = (int(v) for v in parts[1].split("x"))
+            m, kc = b_ * h * w, 9 * int(parts[3]) // 64
+        elif parts[0] == "tconv":
+            b_, f, hw = (int(v) for v in parts[1].split("x"))
+            m, kc = b_ * f * hw, 3 * int(parts[3]) // 64
+        else:
+            m, kc = int(parts[1]), (int(parts[3]) + 63) // 64
+        if m < 4096 or (key in table and not a.retune):
+            continue
+        sk = G.auto_splitk(m, n, kc)
+        res, flops, _ = bench_key(key, only_splitk=sk)
+        (bn, _), us = min(res.items(), key=lambda kv: kv[1])
+        base = min((v for (b2, s2), v in res.items()), default=float("nan"))
+        new[key] = [bn, sk]
+        report.append(dict(key=key, calls=cnt, best=[bn, sk], us=round(us, 2), tflops=round(flops / us / 1e6, 1),
+                           all={f"{b2}/{s2}": round(v, 2) for (b2, s2), v in sorted(res.items())}))
+        print(json.dumps(report[-1]), flush=True)
+    table.update(new)
+    json.dump(report, open(a.out.replace(".json", "_zeroscope.json"), "w"), indent=1)
+    json.dump(table, open("gpurun_out/tuned_sm100.json", "w"), indent=0, sort_keys=True)
+    print(f"tuned {len(new)} shapes; merged table in gpurun_out/tuned_sm100.json", flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "kandinsky2"])
+    ap.add_argument("--model", default="anythingv3", choices=["anythingv3", "kandinsky2", "zeroscopev2xl"])
     ap.add_argument("--retune", action="store_true", help="measure shapes again even if the table has them")
     ap.add_argument("--bands", type=lambda v: [int(x) for x in v.split(",")], default=[2, 4, 8])
     ap.add_argument("--write", action="store_true")
@@ -217,6 +279,8 @@ def main():
         return tune_batched(a)
     if a.model == "kandinsky2":
         return tune_kandinsky(a)
+    if a.model == "zeroscopev2xl":
+        return tune_video(a)
     from arbius_b200.models.sd15.pipeline import SD15Config, SD15Pipeline
     pipe = SD15Pipeline(SD15Config(), backend="native", device="cuda", dtype=torch.float16, use_graph=False)
     G.RECORD = []
