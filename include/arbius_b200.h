@@ -260,6 +260,13 @@ typedef struct {
   const unsigned int* tick; const unsigned int* wait_site; int self_rank;
 } ab_attn_segs_args;
 int ab_flash_attn_segs(const ab_attn_segs_args* args, void* stream);
+/* Profiling aids (never needed for results). ab_gemm_set_debug: a device buffer of >= 8 * grid_size int64; every CTA of
+ * the next tcgen05 GEMM / conv launches writes clock64() offsets {setup, first operands, MMAs issued, accumulator
+ * ready, epilogue done, TMEM released, first chunk in registers, first chunk stored} (scripts/gemm_phases.py).
+ * ab_attn_set_debug: >= 4096 int64; CTA (0,0,0) of the head-dim <= 64 flash attention kernel writes a timeline of its
+ * first 32 KV tiles (scripts/attn_timeline.py). NULL switches either off. Not thread-safe; not for use under capture. */
+void ab_gemm_set_debug(long long* buf);
+void ab_attn_set_debug(long long* buf);
 /* ---- K8: temporal self-attention of the video UNets (csrc/temporal_attn.cu) -----------------------------
  * q/k/v/out are channels-last video tensors [B, F_s, HW, heads*D] (token rows of `row_stride` elements, so q, k, v
  * may be column slices of one fused QKV projection). Every pixel attends over its F frames. With nsrc > 1 the
