@@ -187,6 +187,45 @@ def test_conv3x3_stride2_through_tma_strides_equals_the_gathered_bytes(dt, b, h,
 
 
 @pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("m,n,k,kw", [(4096, 320, 320, {}), (2560 + 77, 640, 640, dict(act="silu")), (3000, 960, 320, dict(res=True)),
+                                       (4096, 2560, 320, dict(geglu=True)), (2048 + 130, 5120, 640, dict(geglu=True, res=True)),
+                                       (1024, 1280, 1280, dict(act="gelu")), (2304, 96, 128, {}), (5000, 352, 192, dict(act="silu", res=True))])
+def test_two_sm_gemm_returns_the_one_sm_bytes(dt, m, n, k, kw):
+    """csrc/gemm_2sm.cu (tcgen05.mma.cta_group::2, M-persistent, TMA-store epilogue) against csrc/gemm_tc.cu: the K order
+    of every output element is the same, so the bytes must be; and both against fp32 PyTorch."""
+    import ctypes as C
+    from arbius_b200 import ops
+    from arbius_b200.ops import native
+    lib = native.load()
+    lib.ab_gemm_set_2sm.argtypes = [C.c_int, C.c_int]
+    lib.ab_gemm_set_2sm.restype = None
+    geglu = kw.get("geglu", False)
+    nout = n // 2 if geglu else n
+    x = torch.randn(m, k, device="cuda", dtype=dt)
+    w = torch.randn(n, k, device="cuda", dtype=dt) / k ** 0.5
+    b = torch.randn(n, device="cuda", dtype=dt)
+    res = torch.randn(m, nout, device="cuda", dtype=dt) if kw.get("res") else None
+    args = dict(geglu=geglu, act=kw.get("act"), residual=res, splitk=1)
+    try:
+        lib.ab_gemm_set_2sm(0, -1)
+        one = ops.gemm(x, w, b, **args)
+        lib.ab_gemm_set_2sm(1, 256)
+        two = ops.gemm(x, w, b, **args)
+    finally:
+        lib.ab_gemm_set_2sm(-1, -1)
+    assert torch.equal(one, two)
+    y = x.float() @ w.float().t() + b.float()
+    if not geglu:
+        if kw.get("act") == "silu":
+            y = F.silu(y)
+        elif kw.get("act") == "gelu":
+            y = F.gelu(y)
+        if res is not None:
+            y = y + res.float()
+        _close(two, y, dt)
+
+
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("n,hw,c1,c2,act", [(2, 4096, 320, 0, "silu"), (2, 1024, 1280, 640, "silu"),
                                             (2, 64, 1280, 1280, None), (1, 16384, 128, 0, "silu"),
                                             (3, 100, 64, 0, None), (2, 256, 1920, 0, "silu")])
