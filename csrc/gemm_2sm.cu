@@ -41,6 +41,13 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* m,
         "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_4d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], "
+        "[%2];\n" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
 __device__ __forceinline__ void umma_ss_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -65,8 +72,8 @@ constexpr int G2_THREADS = 320;
 
 template <int BN, typename T, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G2_THREADS, 1)
-gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ GemmParams p) {
+gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+               const __grid_constant__ CUtensorMap tmB, const __grid_constant__ GemmParams p) {
     constexpr int A_BYTES = BM * BK * 2;                 // this CTA's 128 rows
     constexpr int B_BYTES = (BN / 2) * BK * 2;           // this CTA's half of the weight tile
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -93,11 +100,23 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int pair0 = blockIdx.x >> 1;
     const int pairs = gridDim.x >> 1;
     const int n0 = blockIdx.y * BN;
-    const int kc_end = p.k1_chunks;
+    const int chunks_per_tap = p.k1_chunks + p.k2_chunks;
+    const int kc_end = p.taps * chunks_per_tap;
+    // this CTA's 128-row tile of pair tile tp is M tile 2 * tp + rank; conv modes: a bw x bh x bi pixel box of the images
+    int w0 = 0, h0 = 0, i0 = 0;
+    auto set_tile = [&](int tp) {
+        if (p.conv) {
+            const int tm = 2 * tp + static_cast<int>(rank);
+            w0 = (tm % p.tiles_w) << p.bw_log2;
+            h0 = ((tm / p.tiles_w) % p.tiles_h) << p.bh_log2;
+            i0 = (tm / (p.tiles_w * p.tiles_h)) << (7 - p.bw_log2 - p.bh_log2);
+        }
+    };
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        if (p.k2_chunks) tma_prefetch_desc(&tmA2);
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -127,13 +146,26 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             uint32_t phase = 0;
             for (int tp = pair0; tp < p.tiles_x; tp += pairs) {
                 const int m_row = tp * 2 * BM + static_cast<int>(rank) * BM;
+                set_tile(tp);
+                int tap = 0, cc = 0;
                 for (int kc = 0; kc < kc_end; ++kc) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * STAGE_BYTES;
                     if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);   // both CTAs' bytes land on this barrier
-                    tma_load_2d_2sm(sa, &tmA, &full_bar[stage], kc * BK, m_row);
+                    const bool second = cc >= p.k1_chunks;
+                    const CUtensorMap* ma = second ? &tmA2 : &tmA;
+                    const int c0 = (second ? cc - p.k1_chunks : cc) * BK;
+                    if (p.conv) {
+                        // conv == 1: 3x3 taps; conv == 2: 3x1 taps along H only (temporal conv on [B, F, HW, C])
+                        const int dh = p.conv == 2 ? tap - 1 : tap / 3 - 1;
+                        const int dw = p.conv == 2 ? 0 : tap % 3 - 1;
+                        tma_load_4d_2sm(sa, ma, &full_bar[stage], c0, w0 + dw, h0 + dh, i0);
+                    } else {
+                        tma_load_2d_2sm(sa, ma, &full_bar[stage], c0, m_row);
+                    }
                     tma_load_2d_2sm(sa + A_BYTES, &tmB, &full_bar[stage], kc * BK, n0 + static_cast<int>(rank) * (BN / 2));
                     if (++stage == stages) { stage = 0; phase ^= 1; }
+                    if (++cc == chunks_per_tap) { cc = 0; ++tap; }
                 }
             }
         }
@@ -187,17 +219,41 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait(&acc_full[b], (it >> 1) & 1);
             tc_fence_after();
             const long long row0 = static_cast<long long>(tp) * 2 * BM + static_cast<long long>(rank) * BM;
-            const long long out_row = row0 + r;
-            const bool row_ok = out_row < p.M;
-            uint8_t* const stg = staging + (it & 1) * STG_BYTES;
-            if (p.tma_store && it >= 2) {
-                // this staging buffer was last used two tiles ago: its bulk stores must have finished READING it
-                if (warp == 2) {
-                    if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
-                    __syncwarp();
-                }
-                asm volatile("bar.sync 1, 256;\n" ::: "memory");
+            long long out_row = row0 + r;
+            bool row_ok = out_row < p.M;
+            int grp = 0;
+            if (p.conv) {
+                set_tile(tp);
+                const int ww = w0 + (r & ((1 << p.bw_log2) - 1));
+                const int hh = h0 + ((r >> p.bw_log2) & ((1 << p.bh_log2) - 1));
+                const int ii = i0 + (r >> (p.bw_log2 + p.bh_log2));
+                row_ok = (ww < p.W) && (hh < p.H) && (ii < p.nimg);
+                out_row = (static_cast<long long>(ii) * p.H + hh) * p.W + ww;
+                grp = ii;
             }
+            // the row bias (time embedding of the tile's image): staged with the bias when the tile lies in one image — the
+            // same fp32 order as the one-SM kernel (bias + row bias first, then added to the accumulator) — else per row
+            const bool restage = p.conv && p.rowbias && (p.bw_log2 + p.bh_log2) == 7;
+            const bool rb_global = p.rowbias != nullptr && !restage;
+            if (restage) {
+                const T* bias = reinterpret_cast<const T*>(p.bias);
+                const T* rowbias = reinterpret_cast<const T*>(p.rowbias);
+                for (int n = threadIdx.x - 64; n < BN; n += G2_THREADS - 64) {
+                    float bv = 0.f;
+                    if (n0 + n < p.N) {
+                        if (bias) bv = DT<T>::to_f(bias[n0 + n]);
+                        if (i0 < p.nimg) bv += DT<T>::to_f(rowbias[static_cast<long long>(i0) * p.ldrb + n0 + n]);
+                    }
+                    sbias[n] = bv;
+                }
+            }
+            uint8_t* const stg = staging + (it & 1) * STG_BYTES;
+            if (p.tma_store && it >= 2 && warp == 2) {
+                // this staging buffer was last used two tiles ago: its bulk stores must have finished READING it
+                if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
+                __syncwarp();
+            }
+            if (restage || (p.tma_store && it >= 2)) asm volatile("bar.sync 1, 256;\n" ::: "memory");
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + b * ACC_COLS;
             constexpr int NCHUNK = BN / 32;
             uint32_t raw[2][32];
@@ -214,13 +270,13 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[j & 1][i]);
                     if (p.tma_store && EPI == EPI_GEGLU)      // chunks 2k and 2k+1 fill the halves of output box k
-                        epilogue_chunk32<T, EPI>(p, out_row, 0, n_base, v, sbias + c * 32, false,
+                        epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias + c * 32, rb_global,
                                                  stg + (c >> 1) * (BM * 64) + r * 64, (r >> 1) & 3, (c & 1) * 2);
                     else if (p.tma_store)
-                        epilogue_chunk32<T, EPI>(p, out_row, 0, n_base, v, sbias + c * 32, false, stg + c * (BM * 64) + r * 64,
+                        epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias + c * 32, rb_global, stg + c * (BM * 64) + r * 64,
                                                  (r >> 1) & 3);
                     else
-                        epilogue_chunk32<T, EPI>(p, out_row, 0, n_base, v, sbias + c * 32, false);
+                        epilogue_chunk32<T, EPI>(p, out_row, grp, n_base, v, sbias + c * 32, rb_global);
                 }
             }
             // the accumulator buffer goes back to the leader's MMA lane: one arrival per CTA
@@ -238,7 +294,8 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     } else {
                         for (int c = 0; c < NCHUNK; ++c) {
                             if (n0 + c * 32 >= p.N) break;
-                            tma_store_2d(&p.omap, stg + c * (BM * 64), n0 + c * 32, static_cast<int>(row0));
+                            if (p.conv) tma_store_4d(&p.omap, stg + c * (BM * 64), n0 + c * 32, w0, h0, i0);
+                            else tma_store_2d(&p.omap, stg + c * (BM * 64), n0 + c * 32, static_cast<int>(row0));
                         }
                     }
                     tma_store_commit();
@@ -268,31 +325,62 @@ static int launch_gemm2sm(const ab_gemm_args* a, GemmParams& p, cudaStream_t str
     int stages = 2;
     while (stages < 12 && (stages + 1) * kStage + stg + (2 * (stages + 1) + 4) * 8 + 32 + BN * 4 + 1024 <= 227 * 1024) ++stages;
     const int smem = stages * kStage + stg + (2 * stages + 4) * 8 + 32 + BN * 4 + 1024;
-    if (p.tma_store) {
-        uint64_t dims[2] = {(uint64_t)p.Nout, (uint64_t)a->M};
-        uint64_t str[1] = {(uint64_t)p.ldo * 2};
-        uint32_t box[2] = {32, BM};
-        if (ab_make_tensor_map(&p.omap, a->dtype, 2, a->out, dims, str, box, 64)) return -1;
-    }
-    CUtensorMap tmA, tmB;
-    {
+    const int esz = 2;
+    CUtensorMap tmA, tmA2, tmB;
+    int tiles_m;
+    if (a->conv) {
+        const ConvTile ct = pick_conv_tile(a->H, a->W);
+        p.bw_log2 = ilog2(ct.bw); p.bh_log2 = ilog2(ct.bh);
+        p.tiles_w = (a->W + ct.bw - 1) / ct.bw;
+        p.tiles_h = (a->H + ct.bh - 1) / ct.bh;
+        tiles_m = p.tiles_w * p.tiles_h * ((a->nimg + ct.bi - 1) / ct.bi);
+        uint64_t dims[4] = {(uint64_t)a->K1, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
+        uint64_t str[3] = {(uint64_t)a->K1 * esz, (uint64_t)a->W * a->K1 * esz, (uint64_t)a->H * a->W * a->K1 * esz};
+        uint32_t box[4] = {BK, (uint32_t)ct.bw, (uint32_t)ct.bh, (uint32_t)ct.bi};
+        if (ab_make_tensor_map(&tmA, a->dtype, 4, a->a, dims, str, box, 128)) return -1;
+        tmA2 = tmA;
+        if (a->K2 > 0) {
+            uint64_t dims2[4] = {(uint64_t)a->K2, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
+            uint64_t str2[3] = {(uint64_t)a->K2 * esz, (uint64_t)a->W * a->K2 * esz, (uint64_t)a->H * a->W * a->K2 * esz};
+            if (ab_make_tensor_map(&tmA2, a->dtype, 4, a->a2, dims2, str2, box, 128)) return -1;
+        }
+        if (p.tma_store) {
+            const uint64_t ld = (uint64_t)p.ldo * esz;
+            uint64_t odims[4] = {(uint64_t)a->N, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->nimg};
+            uint64_t ostr[3] = {ld, (uint64_t)a->W * ld, (uint64_t)a->H * a->W * ld};
+            uint32_t obox[4] = {32, (uint32_t)ct.bw, (uint32_t)ct.bh, (uint32_t)ct.bi};
+            if (ab_make_tensor_map(&p.omap, a->dtype, 4, a->out, odims, ostr, obox, 64)) return -1;
+        }
+    } else {
+        tiles_m = (a->M + BM - 1) / BM;
         uint64_t dims[2] = {(uint64_t)a->K1, (uint64_t)a->M};
-        uint64_t str[1] = {(uint64_t)a->K1 * 2};
+        uint64_t str[1] = {(uint64_t)a->K1 * esz};
         uint32_t box[2] = {BK, BM};
         if (ab_make_tensor_map(&tmA, a->dtype, 2, a->a, dims, str, box, 128)) return -1;
-        uint64_t dimsw[2] = {(uint64_t)a->K1, (uint64_t)a->N};
+        tmA2 = tmA;
+        if (p.tma_store) {
+            uint64_t odims[2] = {(uint64_t)p.Nout, (uint64_t)a->M};
+            uint64_t ostr[1] = {(uint64_t)p.ldo * esz};
+            uint32_t obox[2] = {32, BM};
+            if (ab_make_tensor_map(&p.omap, a->dtype, 2, a->out, odims, ostr, obox, 64)) return -1;
+        }
+    }
+    {
+        const uint64_t Kw = (uint64_t)p.taps * (a->K1 + a->K2);
+        uint64_t dimsw[2] = {Kw, (uint64_t)a->N};
+        uint64_t strw[1] = {Kw * esz};
         uint32_t boxw[2] = {BK, BN / 2};
-        if (ab_make_tensor_map(&tmB, a->dtype, 2, a->w, dimsw, str, boxw, 128)) return -1;
+        if (ab_make_tensor_map(&tmB, a->dtype, 2, a->w, dimsw, strw, boxw, 128)) return -1;
     }
     p.stages = stages;
-    p.tiles_x = (a->M + 2 * BM - 1) / (2 * BM);
+    p.tiles_x = (tiles_m + 1) / 2;
     const int n_tiles = (a->N + BN - 1) / BN;
     int pairs = (ab_sm_count() / 2) / n_tiles;
     if (pairs < 1) pairs = 1;
     if (pairs > p.tiles_x) pairs = p.tiles_x;
     if (ab_ensure_max_smem(reinterpret_cast<const void*>(gemm2sm_kernel<BN, T, EPI>), smem)) return -1;
     dim3 grid(2 * pairs, n_tiles, 1);
-    AB_CHECK_CUDA(launch_pdl(gemm2sm_kernel<BN, T, EPI>, grid, dim3(G2_THREADS), smem, stream, tmA, tmB, p));
+    AB_CHECK_CUDA(launch_pdl(gemm2sm_kernel<BN, T, EPI>, grid, dim3(G2_THREADS), smem, stream, tmA, tmA2, tmB, p));
     ab_count_launch(1);
     return 0;
 }
@@ -334,7 +422,9 @@ static int g2_min_rows() {
 extern "C" int ab_gemm_2sm_try(const ab_gemm_args* a, void* stream_) {
     using namespace ab;
     if (!g2_enabled()) return 1;
-    if (a->conv || a->K2 > 0 || a->rowbias || a->splitk > 1 || a->sync_wait || a->halo || a->resample) return 1;
+    if (a->splitk > 1 || a->sync_wait || a->halo || a->resample) return 1;
+    if (!a->conv && (a->K2 > 0 || a->rowbias)) return 1;          // (linear concat / grouped row bias: one-SM kernel)
+    if (a->conv && (a->geglu || a->K2 % BK != 0 || a->M != a->nimg * a->H * a->W)) return 1;
     if (a->K1 % BK != 0 || a->N % 32 != 0 || a->M < g2_min_rows()) return 1;
     if (a->geglu && a->N % 64 != 0) return 1;
     // the tile width is free (it does not change bytes): 256 for wide outputs and for GEGLU (whose bulk stores need whole
@@ -345,16 +435,18 @@ extern "C" int ab_gemm_2sm_try(const ab_gemm_args* a, void* stream_) {
     else if (a->N % 256 == 0) bn = 256;
     else bn = 160;
     GemmParams p{};
-    p.out = a->out; p.bias = a->bias; p.residual = a->residual;
+    p.out = a->out; p.bias = a->bias; p.residual = a->residual; p.rowbias = a->rowbias;
     p.M = a->M; p.N = a->N; p.Nout = a->geglu ? a->N / 2 : a->N;
-    p.k1_chunks = a->K1 / BK; p.taps = 1;
+    p.k1_chunks = a->K1 / BK; p.k2_chunks = a->K2 / BK;
+    p.taps = a->conv == 2 ? 3 : (a->conv ? 9 : 1);
+    p.conv = a->conv; p.nimg = a->nimg; p.H = a->H; p.W = a->W;
     p.act = a->act; p.geglu = a->geglu;
     p.out_scale = a->out_scale == 0.f ? 1.f : a->out_scale;
     p.ldo = a->ldo > 0 ? a->ldo : p.Nout;
     p.ldr = a->ldr > 0 ? a->ldr : p.Nout;
-    p.ldrb = a->N;
+    p.ldrb = a->ldrb > 0 ? a->ldrb : a->N;
     p.splitk = 1;
-    if (p.ldo % 8 != 0 || p.ldr % 8 != 0) return 1;
+    if (p.ldo % 8 != 0 || p.ldr % 8 != 0 || p.ldrb % 8 != 0) return 1;
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     const int rc = a->dtype == AB_BF16 ? dispatch_gemm2sm<__nv_bfloat16>(a, bn, p, stream) : dispatch_gemm2sm<__half>(a, bn, p, stream);
     return rc == 0 ? 0 : -1;

@@ -165,4 +165,22 @@ __device__ __forceinline__ void epilogue_chunk32(const GemmParams& p, long long 
     }
 }
 
+// ---- host side: the 128-pixel conv tile (BW x BH x BI, powers of two) for an H x W image ----
+inline int ilog2(int v) { int l = 0; while ((1 << l) < v) ++l; return l; }
+
+struct ConvTile { int bw, bh, bi; };
+inline ConvTile pick_conv_tile(int H, int W) {
+    // BW: power of two <= 128 with the least padding waste (ties -> larger)
+    int best_bw = 8; double best = 1e9;
+    for (int bw = 128; bw >= 8; bw >>= 1) {
+        double waste = double((W + bw - 1) / bw * bw) / W;
+        if (waste < best - 1e-9) { best = waste; best_bw = bw; }
+    }
+    int bh_max = 128 / best_bw;
+    int bh = 1;
+    while (bh < bh_max && bh < H) bh <<= 1;   // smallest pow2 >= H, capped
+    if (bh > bh_max) bh = bh_max;
+    return {best_bw, bh, 128 / (best_bw * bh)};
+}
+
 }  // namespace ab

@@ -494,23 +494,6 @@ namespace ab {
 
 namespace ab {
 
-static int ilog2(int v) { int l = 0; while ((1 << l) < v) ++l; return l; }
-
-struct ConvTile { int bw, bh, bi; };
-static ConvTile pick_conv_tile(int H, int W) {
-    // BW: power of two <= 128 with the least padding waste (ties -> larger)
-    int best_bw = 8; double best = 1e9;
-    for (int bw = 128; bw >= 8; bw >>= 1) {
-        double waste = double((W + bw - 1) / bw * bw) / W;
-        if (waste < best - 1e-9) { best = waste; best_bw = bw; }
-    }
-    int bh_max = 128 / best_bw;
-    int bh = 1;
-    while (bh < bh_max && bh < H) bh <<= 1;   // smallest pow2 >= H, capped
-    if (bh > bh_max) bh = bh_max;
-    return {best_bw, bh, 128 / (best_bw * bh)};
-}
-
 static int auto_block_n(int M_tiles, int N, bool geglu) {
     // Prefer the tile width that fills 148 SMs x 2 resident CTAs with the least idle tail.
     static const int cands[] = {256, 160, 128, 96, 64, 32};

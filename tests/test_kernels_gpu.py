@@ -226,6 +226,42 @@ def test_two_sm_gemm_returns_the_one_sm_bytes(dt, m, n, k, kw):
 
 
 @pytest.mark.parametrize("dt", DT)
+def test_two_sm_conv_returns_the_one_sm_bytes(dt):
+    """The pair tiles of csrc/gemm_2sm.cu on the implicit-GEMM convs: 3x3 with time-embedding row bias, residual, virtual
+    concat; an odd number of 128-pixel tiles; tiles that span images; the temporal 3x1 conv."""
+    import ctypes as C
+    from arbius_b200 import ops
+    from arbius_b200.ops import native
+    lib = native.load()
+    lib.ab_gemm_set_2sm.argtypes = [C.c_int, C.c_int]
+    lib.ab_gemm_set_2sm.restype = None
+    cases = []
+    for (b, h, w, c1, c2, cout, act) in [(2, 64, 64, 320, 0, 320, "silu"), (3, 24, 40, 128, 64, 192, None), (8, 8, 8, 256, 0, 256, None),
+                                         (5, 16, 16, 128, 128, 160, "silu")]:
+        x1 = torch.randn(b, h, w, c1, device="cuda", dtype=dt)
+        x2 = torch.randn(b, h, w, c2, device="cuda", dtype=dt) if c2 else None
+        wp = ops.pack_conv_weight(torch.randn(cout, c1 + c2, 3, 3, device="cuda", dtype=dt) / (9 * (c1 + c2)) ** 0.5)
+        bias = torch.randn(cout, device="cuda", dtype=dt)
+        temb = torch.randn(b, cout, device="cuda", dtype=dt)
+        res = torch.randn(b, h, w, cout, device="cuda", dtype=dt)
+        cases.append(lambda x1=x1, x2=x2, wp=wp, bias=bias, temb=temb, res=res, act=act:
+                     ops.conv3x3(x1, wp, bias, x2=x2, rowbias=temb, residual=res, act=act, splitk=1))
+    xt = torch.randn(2, 12, 600, 128, device="cuda", dtype=dt)
+    wt = ops.pack_temporal_conv_weight(torch.randn(192, 128, 3, 1, 1, device="cuda", dtype=dt) / (3 * 128) ** 0.5)
+    bt = torch.randn(192, device="cuda", dtype=dt)
+    cases.append(lambda: ops.conv_temporal(xt, wt, bt, splitk=1))
+    for fn in cases:
+        try:
+            lib.ab_gemm_set_2sm(0, -1)
+            one = fn()
+            lib.ab_gemm_set_2sm(1, 256)
+            two = fn()
+        finally:
+            lib.ab_gemm_set_2sm(-1, -1)
+        assert torch.equal(one, two)
+
+
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("n,hw,c1,c2,act", [(2, 4096, 320, 0, "silu"), (2, 1024, 1280, 640, "silu"),
                                             (2, 64, 1280, 1280, None), (1, 16384, 128, 0, "silu"),
                                             (3, 100, 64, 0, None), (2, 256, 1920, 0, "silu")])
