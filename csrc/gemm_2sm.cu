@@ -1,5 +1,6 @@
-// Two-SM tcgen05 GEMM for large plain linear layers: out[M, N] = act(A[M, K] . W[N, K]^T + bias) (+ res),
-// or the GEGLU form. A pair of CTAs on neighbouring SMs (cluster 2 x 1 x 1) owns a 256-row x BN tile:
+// Two-SM tcgen05 GEMM for large linear layers and convs: out[M, N] = act(A[M, K] . W[N, K]^T + bias)
+// (+ res), the GEGLU form, or the implicit-GEMM 3x3 / temporal 3x1 conv (4-D TMA boxes, row bias, virtual concat) of
+// gemm_tc.cu. A pair of CTAs on neighbouring SMs (cluster 2 x 1 x 1) owns a 256-row x BN tile:
 //   * each CTA loads ITS 128 rows of A and ITS HALF of the weight tile (BN / 2 rows) — `tcgen05.mma.cta_group::2` reads
 //     both halves, so per SM the shared-memory traffic per FLOP is what a 128 x 2BN one-SM tile would need;
 //   * the leader CTA's elected lane issues the MMAs for both SMs; each CTA's accumulator (its 128 rows x BN columns)
@@ -425,7 +426,10 @@ extern "C" int ab_gemm_2sm_try(const ab_gemm_args* a, void* stream_) {
     if (a->splitk > 1 || a->sync_wait || a->halo || a->resample) return 1;
     if (!a->conv && (a->K2 > 0 || a->rowbias)) return 1;          // (linear concat / grouped row bias: one-SM kernel)
     if (a->conv && (a->geglu || a->K2 % BK != 0 || a->M != a->nimg * a->H * a->W)) return 1;
-    if (a->K1 % BK != 0 || a->N % 32 != 0 || a->M < g2_min_rows()) return 1;
+    // convs need more rows to fill the 74 pairs evenly: at 32768 rows (four SD tasks at 64 x 64) the one-SM kernel's 128-row
+    // tiles still win, at ZeroScope's 110k-442k rows the pair tiles do (12.91 -> 12.69 s per task)
+    const int min_rows = (a->conv && g2_min_rows_v < 0) ? (g2_min_rows() > 65536 ? g2_min_rows() : 65536) : g2_min_rows();
+    if (a->K1 % BK != 0 || a->N % 32 != 0 || a->M < min_rows) return 1;
     if (a->geglu && a->N % 64 != 0) return 1;
     // the tile width is free (it does not change bytes): 256 for wide outputs and for GEGLU (whose bulk stores need whole
     // 32-column output boxes), 160 where it divides N
