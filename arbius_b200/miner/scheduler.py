@@ -37,11 +37,13 @@ class CostModel:
 
     # ms per task measured on B200 at the template defaults (profiles/multigpu_n8_v1.md); the P=2 rows are
     # the guidance-parallel pair predictors and only count where such a predictor was actually built
-    MEASURED_B200 = {"anythingv3": {1: 127.0, 2: 110.0}, "zeroscopev2xl": {1: 15000.0, 2: 7800.0},
-                     "kandinsky2": {1: 883.0, 2: 703.0}, "damo": {1: 1135.0}}
+    # ms per task, round-2 end state (profiles/bench_r2_n1_v2.json, bench_r2_n8_v0.json latency_mode); the two-GPU
+    # guidance-parallel entries of ZeroScope / Kandinsky are the round-1 ratios applied to the new one-GPU times
+    MEASURED_B200 = {"anythingv3": {1: 116.0, 2: 98.0}, "zeroscopev2xl": {1: 13100.0, 2: 6800.0},
+                     "kandinsky2": {1: 780.0, 2: 620.0}, "damo": {1: 1135.0}}
 
     # ms per task of the frame-parallel text-to-video predictors (tests/mp_frame_parallel.py scaled to 50 steps)
-    MEASURED_B200_FRAMES = {"zeroscopev2xl": {2: 7900.0, 4: 4566.0, 8: 2768.0}, "damo": {2: 993.0}}   # profiles/multigpu_frame_parallel_v0.md
+    MEASURED_B200_FRAMES = {"zeroscopev2xl": {2: 7900.0, 4: 4566.0, 8: 2689.0}, "damo": {2: 993.0}}   # profiles/multigpu_frame_parallel_v0.md, bench_r2_n8_v0.json
 
     @classmethod
     def measured_b200(cls, pair_families: Sequence[str] = (), frame_families: Sequence[str] = (),
