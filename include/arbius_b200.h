@@ -268,7 +268,7 @@ int ab_flash_attn_segs(const ab_attn_segs_args* args, void* stream);
 void ab_gemm_set_debug(long long* buf);
 /* Large plain GEMMs (no conv / concat / row bias / split-K, M >= min_rows) run on the two-SM kernel (csrc/gemm_2sm.cu:
  * tcgen05.mma.cta_group::2 on 256-row tiles, M-persistent, double-buffered accumulators). Same bytes as the one-SM kernel.
- * mode 0 / 1 = off / on, -1 = the default (on unless AB_GEMM_2SM=0); min_rows < 0 = the default (16384). */
+ * mode 0 / 1 = off / on, -1 = the default (on unless AB_GEMM_2SM=0); min_rows < 0 = the default (12288). */
 void ab_gemm_set_2sm(int mode, int min_rows);
 void ab_attn_set_debug(long long* buf);
 /* ---- K8: temporal self-attention of the video UNets (csrc/temporal_attn.cu) -----------------------------
