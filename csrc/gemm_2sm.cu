@@ -423,6 +423,10 @@ static int g2_min_rows() {
 extern "C" int ab_gemm_2sm_try(const ab_gemm_args* a, void* stream_) {
     using namespace ab;
     if (!g2_enabled()) return 1;
+    // anything malformed goes to the one-SM entry point, which owns the argument checks and their error texts
+    if (!a->a || !a->w || !a->out || (a->K2 > 0 && !a->a2) || a->conv < 0 || a->conv > 2 || a->M <= 0 || a->N <= 0 || a->K1 <= 0 ||
+        (a->dtype != AB_F16 && a->dtype != AB_BF16))
+        return 1;
     if (a->splitk > 1 || a->sync_wait || a->halo || a->resample) return 1;
     if (!a->conv && (a->K2 > 0 || a->rowbias)) return 1;          // (linear concat / grouped row bias: one-SM kernel)
     if (a->conv && (a->geglu || a->K2 % BK != 0 || a->M != a->nimg * a->H * a->W)) return 1;
