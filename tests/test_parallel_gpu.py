@@ -128,3 +128,20 @@ def test_patch_parallel_kandinsky_matches_single_gpu_bytes():
     sys.stdout.write(r.stdout[-3000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "bit-identical=False" not in r.stdout and "patch-parallel P=" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_nvls_multimem_broadcast_reaches_every_rank():
+    """parallel/nvls.py: one multimem.st per 16 bytes lands in every GPU's copy of the buffer (VMM memory bound to a
+    multicast object). Skipped where the driver does not offer multicast (no NVSwitch / fabric manager)."""
+    n = min(torch.cuda.device_count(), 8)
+    n = max(p for p in (2, 4, 8) if p <= n)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", "29619", os.path.join(os.path.dirname(HERE), "scripts", "bench_nvls.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=os.path.dirname(HERE))
+    sys.stdout.write(r.stdout[-2000:])
+    if "nvls unsupported" in r.stdout or "nvls setup failed" in r.stdout:
+        pytest.skip(r.stdout.strip().splitlines()[-1])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "received_ok=True" in r.stdout and "received_ok=False" not in r.stdout
