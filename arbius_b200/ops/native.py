@@ -140,6 +140,9 @@ def load() -> C.CDLL:
     _sig(lib.ab_launch_count, ull, [])
     _sig(lib.ab_gemm, i, [C.POINTER(GemmArgs), vp])
     _sig(lib.ab_gemm_workspace_bytes, C.c_size_t, [C.POINTER(GemmArgs)])
+    _sig(lib.ab_gemm_set_2sm, None, [i, i])          # two-SM kernel on / off and its row threshold (tests, A/B timing)
+    _sig(lib.ab_gemm_set_debug, None, [vp])          # profiling hooks: scripts/gemm_phases.py, scripts/attn_timeline.py
+    _sig(lib.ab_attn_set_debug, None, [vp])
     _sig(lib.ab_conv_direct, i, [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp])
     _sig(lib.ab_groupnorm, i, [C.POINTER(GroupNormArgs), vp])
     _sig(lib.ab_groupnorm_partials_bytes, C.c_size_t, [i, i])
