@@ -52,7 +52,7 @@ __global__ void peer_barrier_kernel(PeerFlags f, int rank, int world, unsigned i
         unsigned int v;
         do {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f.flags[rank] + t) : "memory");
-            if (clock64() - t0 > 20000000000LL) { printf("peer barrier timeout rank %d waiting for %d\n", rank, t); __trap(); }
+            if (clock64() - t0 > 120000000000LL) { printf("peer barrier timeout rank %d waiting for %d\n", rank, t); __trap(); }
         } while (static_cast<int>(v - epoch) < 0);
     }
 }
@@ -76,7 +76,7 @@ __global__ void peer_barrier_auto_kernel(PeerFlags f, int rank, int world) {
         unsigned int v;
         do {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f.flags[rank] + 32 + t) : "memory");
-            if (clock64() - t0 > 20000000000LL) { printf("peer barrier (auto) timeout rank %d waiting for %d\n", rank, t); __trap(); }
+            if (clock64() - t0 > 120000000000LL) { printf("peer barrier (auto) timeout rank %d waiting for %d\n", rank, t); __trap(); }
         } while (static_cast<int>(v - epoch) < 0);
     }
 }
